@@ -1,0 +1,147 @@
+/* dvf_b200.h -- C ABI of the B200-native SparseVFC vector-field hot path.
+ *
+ * dynamo (aristoteleo/dynamo-release) has no FFI: its boundary for this path is a set of module-level
+ * Python functions.  Each entry point below replaces the reference function cited
+ * beside it (paths relative to /root/reference/dynamo); the Python host layer in dynamo_release_b200/
+ * binds them with ctypes and mirrors the reference signatures.
+ *
+ * Conventions
+ *   - every pointer named x, Xc, C, Y, U, P, V, J, ... is a DEVICE pointer (float64 unless stated),
+ *     C-contiguous, caller-owned; nothing is allocated behind the caller's back except inside
+ *     dvf_fit_* where the workspace is queried first (dvf_fit_workspace_bytes) and passed in;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *   - all functions return 0 on success, <0 on error; dvf_last_error() gives a thread-local message;
+ *   - sizes: n / N cells, D dimensions (1 <= D <= 64), M control points.
+ */
+#ifndef DVF_B200_H
+#define DVF_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DVF_OK 0
+#define DVF_ERR_ARG (-1)       /* bad argument (shape, NULL pointer, unsupported D) */
+#define DVF_ERR_CUDA (-2)      /* CUDA runtime error, see dvf_last_error() */
+#define DVF_ERR_NUMERIC (-3)   /* solver met a non-positive pivot / EM could not start */
+#define DVF_ERR_COMM (-4)      /* NCCL error */
+#define DVF_ERR_WORKSPACE (-5) /* workspace too small */
+
+int dvf_abi_version(void);
+const char* dvf_last_error(void);
+
+/* K1: K[i, j] = exp(-beta |x_i - Xc_j|^2), row-major n x M with leading dimension ldk (>= M).
+ * replaces vectorfield/utils.py:180-212 (con_K, values path). */
+int dvf_kernel_matrix(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
+                      double* K, int64_t ldk, void* stream);
+
+/* K5: v = K(x, Xc) C  (n x D).   replaces vectorfield/utils.py:73-142 (vector_field_function;
+ * ctrl-point masking and dim slicing are done by the host layer on C / the result). */
+int dvf_eval(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
+             const double* C, double* v, void* stream);
+
+/* K6: J[i, j, c] = -2 beta sum_m C[m, i] k(x_c, Xc_m) (x_c[j] - Xc[m, j]); layout (D, D, n), cell index
+ * fastest.  replaces vectorfield/utils.py:351-379 (Jacobian_rkhs_gaussian). */
+int dvf_jacobian(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
+                 const double* C, double* J, void* stream);
+
+/* K7: fused divergence / acceleration / curvature without materialising J.  Any output may be NULL.
+ *   v (n x D) = f(x);  div (n) = tr J;  acc (n x D) = J v;  acc_norm (n) = |acc|;
+ *   formula 2: curv (n x D) = (a (v.v) - v (v.a)) / |v|^4, curv_norm = |curv|;
+ *   formula 1: curv_norm = |v a^T|_F / |v|^3, curv untouched.
+ * replaces vectorfield/utils.py:699-725, 728-793, 743-757, 797-821. */
+int dvf_div_acc_curv(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
+                     const double* C, int formula, double* v, double* div, double* acc,
+                     double* acc_norm, double* curv, double* curv_norm, void* stream);
+
+/* K8: out[e, r, c] = float32( Qe[e, :] J[:, :, c] Qr[r, :]^T ), J laid out (D, D, n), out (Ge, Gr, n).
+ * If take_abs != 0 the absolute value is taken before any reduction.  If group != NULL (int32 label per
+ * cell, 0 <= label < n_groups) the per-group SUM over cells of the float32-rounded values is accumulated in
+ * float64 into out_group_sum (n_groups x Ge x Gr, must be zeroed by the caller).  out_full may be NULL.
+ * replaces vectorfield/utils.py:544-554 (transform_jacobian), :497-541, and for Ge=Gr=1 with
+ * out_elem (float64, n) :430-453 (elementwise_jacobian_transformation). */
+int dvf_gene_transform(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr,
+                       int Gr, int take_abs, const int32_t* group, int n_groups, float* out_full,
+                       double* out_group_sum, void* stream);
+int dvf_gene_transform_elem(const double* J, int64_t n, int D, const double* qe, const double* qr,
+                            double* out_elem, void* stream);
+
+/* K16: out (n x G) = V (n x D) Q^T, Q is (G x D).   replaces vectorfield/utils.py:311-326. */
+int dvf_vector_transform(const double* V, int64_t n, int D, const double* Q, int G, double* out,
+                         void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * SparseVFC EM fit (vectorfield/scVectorField.py:417-497; Gaussian kernel branch)
+ * ------------------------------------------------------------------------------------------- */
+typedef struct dvf_em_params {
+    double a;        /* outlier uniform-distribution volume, default 5            (:315) */
+    double gamma;    /* initial inlier fraction, default 0.9                       (:318) */
+    double lambda_;  /* regularisation weight, default 3                           (:319) */
+    double minP;     /* posterior floor, default 1e-5                              (:320) */
+    double ecr;      /* energy change-rate stop criterion, default 1e-5            (:317) */
+    double theta;    /* inlier threshold on P, default 0.75                        (:322) */
+    int max_iter;    /* MaxIter, default 500 (30 through VectorField)              (:321) */
+    int check_every; /* iterations launched between host reads of the stop flag; 0 = default (8) */
+} dvf_em_params;
+
+/* scalars the EM loop leaves on the host when it returns */
+typedef struct dvf_em_result {
+    int n_iter;          /* number of loop bodies executed (reference `i` at exit)             */
+    int status;          /* 0 ok, DVF_ERR_NUMERIC if the solver failed                          */
+    double sigma2;       /* final sigma2                                               (:486)   */
+    double gamma;        /* final gamma                                                (:489)   */
+    double n_inlier;     /* #(P > theta) of the last iteration, global over ranks               */
+} dvf_em_result;
+
+/* width (in doubles) of one row of the fused [U | Y | 0-pad] matrix for given M, D */
+int64_t dvf_fit_row_width(int M, int D);
+/* bytes of workspace dvf_fit_em needs for N_local cells (includes the N_local x width U matrix) */
+int dvf_fit_workspace_bytes(int64_t N_local, int D, int M, size_t* out);
+
+/* Whole EM loop on the device.  X, Y: this rank's cells (N_local x D); N_total: cells over all ranks;
+ * Xc: control points (M x D); on return C (M x D), P (N_local, clamped >= minP), V (N_local x D) = U C,
+ * E_traj / tecr_traj (max_iter doubles each, first n_iter valid).  comm: handle from dvf_comm_init or NULL
+ * (single GPU).  The stop flag is read back every `check_every` iterations; kernels launched after the
+ * flag is raised exit immediately.  replaces scVectorField.py:417-497 and tools/utils.py:2948-2981. */
+int dvf_fit_em(const double* X, const double* Y, int64_t N_local, int64_t N_total, int D,
+               const double* Xc, int M, double beta, const dvf_em_params* prm, double* C, double* P,
+               double* V, double* E_traj, double* tecr_traj, dvf_em_result* res, void* ws,
+               size_t ws_bytes, void* comm, void* stream);
+
+/* Step-level entry points (used by the teacher-forced parity tests; the loop above is built from them).
+ *   UY is the N x W row-major matrix [U | Y | 0], W = dvf_fit_row_width(M, D).                       */
+int dvf_build_uy(const double* X, const double* Y, int64_t N, int D, const double* Xc, int M,
+                 double beta, double* UY, void* stream);
+/* E-step, scVectorField.py:197-227: r2 (N) -> P (N, unclamped) ; stats[0..3] = {sum P r2/(2 sigma2) +
+ * sum P log(sigma2) D/2 (= E of get_P), sum P, min nonzero t1, number of exact zeros}. */
+int dvf_estep(const double* r2, int64_t N, int D, double sigma2, double gamma, double a, double* P,
+              double* stats, void* stream);
+/* M-step assembly, scVectorField.py:468-476: G (W x W, lower triangle valid) = UY^T diag(max(P, minP)) UY.
+ * scratch: dvf_gram_scratch_bytes(). */
+int dvf_gram_scratch_bytes(int64_t N, int D, int M, size_t* out);
+int dvf_gram(const double* UY, const double* P, double minP, int64_t N, int D, int M, double* G,
+             void* scratch, size_t scratch_bytes, void* stream);
+/* Solve (G[:M,:M] + lam_sigma2 * Kc) C = G[M:M+D, :M]^T.  scVectorField.py:475-481; see DESIGN.md for the
+ * choice of a Cholesky solve of the M x M system instead of the reference's normal equations.
+ * L: M x M scratch.  info (device int): 0 ok, k>0 = non-positive pivot at column k-1. */
+int dvf_solve(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
+              double* L, double* C, int* info, void* stream);
+/* V = U C, r2 = |Y - V|^2 per cell, stats[0] = sum_n max(P,minP)_n r2_n.   scVectorField.py:484-486 */
+int dvf_update_v(const double* UY, const double* C, const double* P, double minP, int64_t N, int D,
+                 int M, double* V, double* r2, double* stats, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * multi-GPU: one NCCL communicator owned by the library (cells sharded over ranks; the only traffic is
+ * the allreduce of the Gram/RHS block and a few scalars per EM iteration)
+ * ------------------------------------------------------------------------------------------- */
+int dvf_comm_unique_id(void* out128);                          /* rank 0: 128-byte ncclUniqueId */
+int dvf_comm_init(const void* id128, int rank, int world, void** comm);
+int dvf_comm_destroy(void* comm);
+int dvf_comm_allreduce_sum(void* comm, double* buf, int64_t count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
