@@ -1,0 +1,295 @@
+// K1 (Gaussian kernel matrix / fused [U | Y | 0] build), K5 (field evaluation), K7 (fused divergence /
+// acceleration / curvature).  FP64 throughout; control points and coefficients are staged in shared
+// memory in chunks and broadcast to the threads, cells stream from HBM.
+#include "common.cuh"
+
+namespace dvf {
+
+// ------------------------------------------------------------------------------------------------
+// K1: 64 cells x 64 ctrl points per CTA pass, 4 x 4 register tile per thread, runtime D in chunks of 32.
+// Direct form |x - c|^2 = sum_d (x_d - c_d)^2 as scipy cdist does (reference utils.py:195) -- no
+// |x|^2 + |c|^2 - 2 x.c cancellation.
+// ------------------------------------------------------------------------------------------------
+constexpr int K1_T = 64, K1_DC = 32;
+
+__global__ void __launch_bounds__(256) k_kernel_matrix(const double* __restrict__ x, int64_t n, int D,
+                                                       const double* __restrict__ Xc, int M, double beta,
+                                                       double* __restrict__ K, int64_t ldk,
+                                                       const double* __restrict__ Y, int ycols, int padcols) {
+    __shared__ double xs[K1_DC][K1_T + 4];
+    __shared__ double cs[K1_DC][K1_T + 4];
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const int64_t n0 = (int64_t)blockIdx.x * K1_T;
+    for (int m0 = 0; m0 < M; m0 += K1_T) {
+        double acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+        for (int d0 = 0; d0 < D; d0 += K1_DC) {
+            __syncthreads();
+            for (int e = threadIdx.x; e < K1_T * K1_DC; e += 256) {
+                int r = e / K1_DC, d = e % K1_DC;
+                int64_t gn = n0 + r;
+                int gm = m0 + r;
+                xs[d][r] = (gn < n && d0 + d < D) ? x[gn * D + d0 + d] : 0.0;
+                cs[d][r] = (gm < M && d0 + d < D) ? Xc[(int64_t)gm * D + d0 + d] : 0.0;
+            }
+            __syncthreads();
+            const int dl = min(K1_DC, D - d0);
+            for (int d = 0; d < dl; ++d) {
+                double xv[4], cv[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { xv[i] = xs[d][ty * 4 + i]; cv[i] = cs[d][tx * 4 + i]; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { double t = xv[i] - cv[j]; acc[i][j] = fma(t, t, acc[i][j]); }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int64_t gn = n0 + ty * 4 + i;
+            if (gn >= n) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                int gm = m0 + tx * 4 + j;
+                if (gm < M) K[gn * ldk + gm] = exp(-beta * acc[i][j]);
+            }
+        }
+    }
+    // fused [U | Y | 0]: copy Y and zero the padding columns (only when building the fit matrix)
+    if (Y != nullptr) {
+        const int extra = ycols + padcols;
+        for (int e = threadIdx.x; e < K1_T * extra; e += 256) {
+            int r = e / extra, c = e % extra;
+            int64_t gn = n0 + r;
+            if (gn < n) K[gn * ldk + M + c] = (c < ycols) ? Y[gn * ycols + c] : 0.0;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5 / K7: one thread per cell; x, v (and a) live in registers (DP = D padded, compile time); control
+// points and coefficients are read from shared memory with warp-wide broadcast loads.
+// ------------------------------------------------------------------------------------------------
+// ctrl points per shared-memory chunk: 2 x 16 KB of static shared memory whatever DP is
+template <int DP> struct ev_chunk { static constexpr int MC = 2048 / DP; };
+
+template <int DP>
+__device__ __forceinline__ void load_chunk(double* cs, double* Cs, const double* Xc, const double* C, int D,
+                                           int m0, int mc) {
+    for (int e = threadIdx.x; e < mc * DP; e += blockDim.x) {
+        int r = e / DP, d = e % DP;
+        bool ok = d < D;
+        cs[e] = ok ? Xc[(int64_t)(m0 + r) * D + d] : 0.0;
+        Cs[e] = ok ? C[(int64_t)(m0 + r) * D + d] : 0.0;
+    }
+}
+
+template <int DP>
+__global__ void __launch_bounds__(128) k_eval(const double* __restrict__ x, int64_t n, int D,
+                                              const double* __restrict__ Xc, int M, double beta,
+                                              const double* __restrict__ C, double* __restrict__ v) {
+    __shared__ double cs[ev_chunk<DP>::MC * DP];
+    __shared__ double Cs[ev_chunk<DP>::MC * DP];
+    const int64_t cell = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = cell < n;
+    double xr[DP], vr[DP];
+#pragma unroll
+    for (int d = 0; d < DP; ++d) { xr[d] = (live && d < D) ? x[cell * D + d] : 0.0; vr[d] = 0.0; }
+    for (int m0 = 0; m0 < M; m0 += ev_chunk<DP>::MC) {
+        const int mc = min(ev_chunk<DP>::MC, M - m0);
+        __syncthreads();
+        load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
+        __syncthreads();
+        for (int m = 0; m < mc; ++m) {
+            double d2 = 0.0;
+#pragma unroll
+            for (int d = 0; d < DP; ++d) { double t = xr[d] - cs[m * DP + d]; d2 = fma(t, t, d2); }
+            const double k = exp(-beta * d2);
+#pragma unroll
+            for (int d = 0; d < DP; ++d) vr[d] = fma(k, Cs[m * DP + d], vr[d]);
+        }
+    }
+    if (live) {
+#pragma unroll
+        for (int d = 0; d < DP; ++d)
+            if (d < D) v[cell * D + d] = vr[d];
+    }
+}
+
+template <int DP>
+__global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64_t n, int D,
+                                             const double* __restrict__ Xc, int M, double beta,
+                                             const double* __restrict__ C, int formula, double* __restrict__ v_out,
+                                             double* __restrict__ div_out, double* __restrict__ acc_out,
+                                             double* __restrict__ accn_out, double* __restrict__ curv_out,
+                                             double* __restrict__ curvn_out) {
+    __shared__ double cs[ev_chunk<DP>::MC * DP];
+    __shared__ double Cs[ev_chunk<DP>::MC * DP];
+    const int64_t cell = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = cell < n;
+    double xr[DP], vr[DP];
+#pragma unroll
+    for (int d = 0; d < DP; ++d) { xr[d] = (live && d < D) ? x[cell * D + d] : 0.0; vr[d] = 0.0; }
+    double div = 0.0;
+    // pass 1: v = sum_m k_m C_m ; div = -2 beta sum_m k_m C_m . (x - c_m)
+    for (int m0 = 0; m0 < M; m0 += ev_chunk<DP>::MC) {
+        const int mc = min(ev_chunk<DP>::MC, M - m0);
+        __syncthreads();
+        load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
+        __syncthreads();
+        for (int m = 0; m < mc; ++m) {
+            double d2 = 0.0, t2 = 0.0;
+#pragma unroll
+            for (int d = 0; d < DP; ++d) {
+                double t = xr[d] - cs[m * DP + d];
+                d2 = fma(t, t, d2);
+                t2 = fma(t, Cs[m * DP + d], t2);
+            }
+            const double k = exp(-beta * d2);
+            div = fma(k, t2, div);
+#pragma unroll
+            for (int d = 0; d < DP; ++d) vr[d] = fma(k, Cs[m * DP + d], vr[d]);
+        }
+    }
+    div *= -2.0 * beta;
+    const bool need_acc = acc_out || accn_out || curv_out || curvn_out;
+    double ar[DP];
+#pragma unroll
+    for (int d = 0; d < DP; ++d) ar[d] = 0.0;
+    if (need_acc) {
+        // pass 2: a = J v = -2 beta sum_m k_m ((x - c_m) . v) C_m
+        for (int m0 = 0; m0 < M; m0 += ev_chunk<DP>::MC) {
+            const int mc = min(ev_chunk<DP>::MC, M - m0);
+            __syncthreads();
+            load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
+            __syncthreads();
+            for (int m = 0; m < mc; ++m) {
+                double d2 = 0.0, s = 0.0;
+#pragma unroll
+                for (int d = 0; d < DP; ++d) {
+                    double t = xr[d] - cs[m * DP + d];
+                    d2 = fma(t, t, d2);
+                    s = fma(t, vr[d], s);
+                }
+                const double ks = exp(-beta * d2) * s;
+#pragma unroll
+                for (int d = 0; d < DP; ++d) ar[d] = fma(ks, Cs[m * DP + d], ar[d]);
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < DP; ++d) ar[d] *= -2.0 * beta;
+    }
+    if (!live) return;
+    if (v_out) {
+#pragma unroll
+        for (int d = 0; d < DP; ++d)
+            if (d < D) v_out[cell * D + d] = vr[d];
+    }
+    if (div_out) div_out[cell] = div;
+    if (!need_acc) return;
+    double vv = 0.0, va = 0.0, aa = 0.0;
+#pragma unroll
+    for (int d = 0; d < DP; ++d) { vv = fma(vr[d], vr[d], vv); va = fma(vr[d], ar[d], va); aa = fma(ar[d], ar[d], aa); }
+    if (acc_out) {
+#pragma unroll
+        for (int d = 0; d < DP; ++d)
+            if (d < D) acc_out[cell * D + d] = ar[d];
+    }
+    if (accn_out) accn_out[cell] = sqrt(aa);
+    if (formula == 2) {
+        // reference utils.py:752-757: (a (v.v) - v (v.a)) / |v|^4
+        const double nv = sqrt(vv);
+        const double den = (nv * nv) * (nv * nv);
+        double kk = 0.0;
+#pragma unroll
+        for (int d = 0; d < DP; ++d) {
+            double c = (ar[d] * vv - vr[d] * va) / den;   // padded dims: a = v = 0 -> c = 0
+            if (curv_out && d < D) curv_out[cell * D + d] = c;
+            kk = fma(c, c, kk);
+        }
+        if (curvn_out) curvn_out[cell] = sqrt(kk);
+    } else if (curvn_out) {
+        // reference utils.py:743-749: |outer(v, a)|_F / |v|^3 = |v| |a| / |v|^3
+        const double nv = sqrt(vv);
+        curvn_out[cell] = sqrt(vv * aa) / (nv * nv * nv);
+    }
+}
+
+template <typename F>
+static int dispatch_dp(int D, F&& f) {
+    if (D <= 2) return f(std::integral_constant<int, 2>());
+    if (D <= 4) return f(std::integral_constant<int, 4>());
+    if (D <= 8) return f(std::integral_constant<int, 8>());
+    if (D <= 16) return f(std::integral_constant<int, 16>());
+    if (D <= 24) return f(std::integral_constant<int, 24>());
+    if (D <= 32) return f(std::integral_constant<int, 32>());
+    if (D <= 40) return f(std::integral_constant<int, 40>());
+    if (D <= 48) return f(std::integral_constant<int, 48>());
+    return f(std::integral_constant<int, 64>());
+}
+
+}  // namespace dvf
+
+using namespace dvf;
+
+static int check_field_args(const void* x, int64_t n, int D, const void* Xc, int M) {
+    DVF_ARG(n >= 0 && M >= 1, "n=%lld M=%d: need n >= 0, M >= 1", (long long)n, M);
+    DVF_ARG(D >= 1 && D <= kMaxD, "D=%d unsupported (1..%d)", D, kMaxD);
+    DVF_ARG((x || n == 0) && Xc, "NULL pointer");
+    return DVF_OK;
+}
+
+extern "C" int dvf_kernel_matrix(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
+                                 double* K, int64_t ldk, void* stream) {
+    DVF_ARG(n >= 0 && M >= 1 && D >= 1, "bad shape n=%lld D=%d M=%d", (long long)n, D, M);
+    DVF_ARG(ldk >= M && K && Xc, "ldk < M or NULL pointer");
+    if (n == 0) return DVF_OK;
+    k_kernel_matrix<<<(unsigned)((n + K1_T - 1) / K1_T), 256, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, K, ldk,
+                                                                                       nullptr, 0, 0);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}
+
+extern "C" int dvf_build_uy(const double* X, const double* Y, int64_t N, int D, const double* Xc, int M,
+                            double beta, double* UY, void* stream) {
+    if (int rc = check_field_args(X, N, D, Xc, M)) return rc;
+    DVF_ARG(Y && UY, "NULL pointer");
+    if (N == 0) return DVF_OK;
+    const int64_t W = dvf_fit_row_width(M, D);
+    k_kernel_matrix<<<(unsigned)((N + K1_T - 1) / K1_T), 256, 0, (cudaStream_t)stream>>>(X, N, D, Xc, M, beta, UY, W, Y,
+                                                                                       D, (int)(W - M - D));
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}
+
+extern "C" int dvf_eval(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
+                        const double* C, double* v, void* stream) {
+    if (int rc = check_field_args(x, n, D, Xc, M)) return rc;
+    DVF_ARG(C && (v || n == 0), "NULL pointer");
+    if (n == 0) return DVF_OK;
+    return dispatch_dp(D, [&](auto dp) {
+        constexpr int DP = decltype(dp)::value;
+        k_eval<DP><<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, v);
+        DVF_LAUNCH_CHECK();
+        return DVF_OK;
+    });
+}
+
+extern "C" int dvf_div_acc_curv(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
+                                const double* C, int formula, double* v, double* div, double* acc,
+                                double* acc_norm, double* curv, double* curv_norm, void* stream) {
+    if (int rc = check_field_args(x, n, D, Xc, M)) return rc;
+    DVF_ARG(C, "NULL pointer");
+    DVF_ARG(formula == 1 || formula == 2, "formula must be 1 or 2");
+    if (n == 0) return DVF_OK;
+    return dispatch_dp(D, [&](auto dp) {
+        constexpr int DP = decltype(dp)::value;
+        k_dac<DP><<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, formula, v, div,
+                                                                              acc, acc_norm, curv, curv_norm);
+        DVF_LAUNCH_CHECK();
+        return DVF_OK;
+    });
+}

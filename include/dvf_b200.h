@@ -120,12 +120,15 @@ int dvf_estep(const double* r2, int64_t N, int D, double sigma2, double gamma, d
               double* stats, void* stream);
 /* M-step assembly, scVectorField.py:468-476: G (W x W, lower triangle valid) = UY^T diag(max(P, minP)) UY.
  * scratch: dvf_gram_scratch_bytes(). */
+/* G is ldg x ldg with ldg = dvf_gram_ld(D, M) >= W (row-major; only lower-triangular tiles are written).
+ * P must be 16-byte aligned and readable up to an even element count (allocate N + 1 doubles if N is odd). */
+int dvf_gram_ld(int D, int M);
 int dvf_gram_scratch_bytes(int64_t N, int D, int M, size_t* out);
 int dvf_gram(const double* UY, const double* P, double minP, int64_t N, int D, int M, double* G,
              void* scratch, size_t scratch_bytes, void* stream);
 /* Solve (G[:M,:M] + lam_sigma2 * Kc) C = G[M:M+D, :M]^T.  scVectorField.py:475-481; see DESIGN.md for the
  * choice of a Cholesky solve of the M x M system instead of the reference's normal equations.
- * L: M x M scratch.  info (device int): 0 ok, k>0 = non-positive pivot at column k-1. */
+ * L: (M + D) x M scratch.  info (device int): 0 ok, k>0 = non-positive pivot at column k-1. */
 int dvf_solve(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
               double* L, double* C, int* info, void* stream);
 /* V = U C, r2 = |Y - V|^2 per cell, stats[0] = sum_n max(P,minP)_n r2_n.   scVectorField.py:484-486 */
