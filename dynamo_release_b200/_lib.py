@@ -37,6 +37,8 @@ _p, _i, _i64, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_size_t
 SIGNATURES = {
     "dvf_abi_version": (_i, []),
     "dvf_last_error": (C.c_char_p, []),
+    "dvf_profile_enable": (_i, [_i]),
+    "dvf_profile_get": (_i, [C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(C.c_longlong)]),
     "dvf_kernel_matrix": (_i, [_p, _i64, _i, _p, _i, _d, _p, _i64, _p]),
     "dvf_eval": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
     "dvf_jacobian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),

@@ -14,6 +14,9 @@ namespace dvf {
 
 // ---- error plumbing -------------------------------------------------------------------------
 void set_error(const char* fmt, ...);
+// optional CUDA-event timing of the Gram kernel inside dvf_fit_em (dvf_profile_enable)
+void profile_gram_begin(cudaStream_t st);
+void profile_gram_end(cudaStream_t st);
 int cuda_fail(cudaError_t e, const char* what, int line);
 
 #define DVF_CUDA(x)                                                        \
@@ -21,7 +24,14 @@ int cuda_fail(cudaError_t e, const char* what, int line);
         cudaError_t e__ = (x);                                             \
         if (e__ != cudaSuccess) return dvf::cuda_fail(e__, #x, __LINE__);  \
     } while (0)
-#define DVF_LAUNCH_CHECK() DVF_CUDA(cudaGetLastError())
+// every kernel launch of the library goes through this macro: it also feeds the launch counter that
+// bench.py reports as gpu_launches (dvf_profile_get)
+extern long long g_launch_count;
+#define DVF_LAUNCH_CHECK()              \
+    do {                                \
+        ++dvf::g_launch_count;          \
+        DVF_CUDA(cudaGetLastError());   \
+    } while (0)
 #define DVF_ARG(cond, ...)                                                 \
     do {                                                                   \
         if (!(cond)) { dvf::set_error(__VA_ARGS__); return DVF_ERR_ARG; }  \

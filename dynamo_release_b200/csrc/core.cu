@@ -14,7 +14,51 @@ int cuda_fail(cudaError_t e, const char* what, int line) {
     set_error("CUDA error '%s' (%d) in %s at line %d", cudaGetErrorString(e), (int)e, what, line);
     return DVF_ERR_CUDA;
 }
+long long g_launch_count = 0;
+
+// ---- CUDA-event profile of the Gram launches (the dominant kernel) -----------------------------------
+static bool g_prof_on = false;
+static const int kMaxProf = 1024;
+static cudaEvent_t g_ev0[kMaxProf], g_ev1[kMaxProf];
+static int g_ev_made = 0, g_ev_used = 0;
+
+void profile_gram_begin(cudaStream_t st) {
+    if (!g_prof_on || g_ev_used >= kMaxProf) return;
+    if (g_ev_used >= g_ev_made) {
+        cudaEventCreate(&g_ev0[g_ev_made]);
+        cudaEventCreate(&g_ev1[g_ev_made]);
+        ++g_ev_made;
+    }
+    cudaEventRecord(g_ev0[g_ev_used], st);
+}
+void profile_gram_end(cudaStream_t st) {
+    if (!g_prof_on || g_ev_used >= kMaxProf) return;
+    cudaEventRecord(g_ev1[g_ev_used], st);
+    ++g_ev_used;
+}
 }  // namespace dvf
+
+extern "C" int dvf_profile_enable(int on) {
+    dvf::g_prof_on = on != 0;
+    dvf::g_ev_used = 0;
+    dvf::g_launch_count = 0;
+    return DVF_OK;
+}
+
+// gram_ms: summed duration of the recorded Gram launches (kernel + fixed-order reduce); call after the stream
+// has been synchronised.  Launches of EM iterations that ran after the stop flag was raised return at once and
+// are included (they cost microseconds).
+extern "C" int dvf_profile_get(double* gram_ms, int* gram_launches, long long* kernel_launches) {
+    double total = 0.0;
+    for (int i = 0; i < dvf::g_ev_used; ++i) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, dvf::g_ev0[i], dvf::g_ev1[i]) == cudaSuccess) total += ms;
+    }
+    if (gram_ms) *gram_ms = total;
+    if (gram_launches) *gram_launches = dvf::g_ev_used;
+    if (kernel_launches) *kernel_launches = dvf::g_launch_count;
+    return DVF_OK;
+}
 
 extern "C" int dvf_abi_version(void) { return 1; }
 extern "C" const char* dvf_last_error(void) { return dvf::g_err; }

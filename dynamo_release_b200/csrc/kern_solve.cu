@@ -183,6 +183,7 @@ int solve_run(const double* G, int64_t ldg, const double* Kc, int M, int D, doub
     if (grid > want) grid = want < 8 ? 8 : want;
     if (grid > max_grid) grid = max_grid;
     void* params[] = {&a};
+    ++g_launch_count;
     DVF_CUDA(cudaLaunchCooperativeKernel((void*)k_chol_solve, dim3(grid), dim3(256), params, 0, st));
     return DVF_OK;
 }

@@ -1,0 +1,161 @@
+"""Device-level wrappers: CUDA tensors in, CUDA tensors out, one C-ABI call each (include/dvf_b200.h)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from .device import dev, empty, lib, ptr, stream_ptr
+
+MAX_D = 64
+
+
+def _field(x, Xc, Cm=None):
+    x, Xc = dev(x), dev(Xc)
+    if x.dim() != 2 or Xc.dim() != 2 or x.shape[1] != Xc.shape[1]:
+        raise ValueError("x must be (n, D) and X_ctrl (M, D): got %s and %s" % (tuple(x.shape), tuple(Xc.shape)))
+    if Cm is not None:
+        Cm = dev(Cm)
+        if tuple(Cm.shape) != tuple(Xc.shape):
+            raise ValueError("C must have the shape of X_ctrl")
+    return x, Xc, Cm
+
+
+def kernel_matrix(x, Xc, beta):
+    """K1 -- reference vectorfield/utils.py:180-212 (con_K values)."""
+    x, Xc, _ = _field(x, Xc)
+    n, D = x.shape
+    M = Xc.shape[0]
+    K = empty((n, M))
+    _lib.check(lib().dvf_kernel_matrix(ptr(x), n, D, ptr(Xc), M, float(beta), ptr(K), M, stream_ptr()))
+    return K
+
+
+def eval_field(x, Xc, beta, Cm):
+    """K5 -- reference vectorfield/utils.py:73-142."""
+    x, Xc, Cm = _field(x, Xc, Cm)
+    n, D = x.shape
+    v = empty((n, D))
+    _lib.check(lib().dvf_eval(ptr(x), n, D, ptr(Xc), Xc.shape[0], float(beta), ptr(Cm), ptr(v), stream_ptr()))
+    return v
+
+
+def jacobian(x, Xc, beta, Cm, out=None):
+    """K6 -- reference vectorfield/utils.py:351-379; returns (D, D, n)."""
+    x, Xc, Cm = _field(x, Xc, Cm)
+    n, D = x.shape
+    J = empty((D, D, n)) if out is None else out
+    _lib.check(lib().dvf_jacobian(ptr(x), n, D, ptr(Xc), Xc.shape[0], float(beta), ptr(Cm), ptr(J), stream_ptr()))
+    return J
+
+
+def div_acc_curv(x, Xc, beta, Cm, formula=2, want=("v", "div", "acc", "acc_norm", "curv", "curv_norm")):
+    """K7 -- reference vectorfield/utils.py:699-821; returns a dict of the requested outputs."""
+    x, Xc, Cm = _field(x, Xc, Cm)
+    n, D = x.shape
+    shapes = {"v": (n, D), "div": (n,), "acc": (n, D), "acc_norm": (n,), "curv": (n, D), "curv_norm": (n,)}
+    out = {k: (empty(shapes[k]) if k in want else None) for k in shapes}
+    if formula == 1:
+        out["curv"] = None
+    _lib.check(lib().dvf_div_acc_curv(ptr(x), n, D, ptr(Xc), Xc.shape[0], float(beta), ptr(Cm), int(formula),
+                                      ptr(out["v"]), ptr(out["div"]), ptr(out["acc"]), ptr(out["acc_norm"]),
+                                      ptr(out["curv"]), ptr(out["curv_norm"]), stream_ptr()))
+    return out
+
+
+def gene_transform(J, Qe, Qr, take_abs=False, group=None, n_groups=0, full=True):
+    """K8 -- reference vectorfield/utils.py:544-554.  J (D, D, n) -> float32 (Ge, Gr, n) and/or group sums."""
+    J, Qe, Qr = dev(J), dev(Qe), dev(Qr)
+    D, _, n = J.shape
+    Ge, Gr = Qe.shape[0], Qr.shape[0]
+    out = empty((Ge, Gr, n), torch.float32) if full else None
+    gsum = None
+    if group is not None:
+        group = dev(group, torch.int32)
+        gsum = torch.zeros((n_groups, Ge, Gr), dtype=torch.float64, device="cuda")
+    _lib.check(lib().dvf_gene_transform(ptr(J), n, D, ptr(Qe), Ge, ptr(Qr), Gr, int(bool(take_abs)), ptr(group),
+                                        int(n_groups), ptr(out), ptr(gsum), stream_ptr()))
+    return out, gsum
+
+
+def gene_transform_elem(J, qe, qr):
+    """reference vectorfield/utils.py:430-453."""
+    J, qe, qr = dev(J), dev(qe), dev(qr)
+    D, _, n = J.shape
+    out = empty((n,))
+    _lib.check(lib().dvf_gene_transform_elem(ptr(J), n, D, ptr(qe), ptr(qr), ptr(out), stream_ptr()))
+    return out
+
+
+def vector_transform(V, Q):
+    """reference vectorfield/utils.py:311-326:  V Q^T."""
+    V, Q = dev(V), dev(Q)
+    n, D = V.shape
+    G = Q.shape[0]
+    out = empty((n, G))
+    _lib.check(lib().dvf_vector_transform(ptr(V), n, D, ptr(Q), G, ptr(out), stream_ptr()))
+    return out
+
+
+# ---- EM pieces ------------------------------------------------------------------------------------
+def row_width(M, D):
+    return int(_lib.load().dvf_fit_row_width(int(M), int(D)))
+
+
+def build_uy(X, Y, Xc, beta):
+    X, Xc, _ = _field(X, Xc)
+    Y = dev(Y)
+    N, D = X.shape
+    M = Xc.shape[0]
+    UY = empty((N, row_width(M, D)))
+    _lib.check(lib().dvf_build_uy(ptr(X), ptr(Y), N, D, ptr(Xc), M, float(beta), ptr(UY), stream_ptr()))
+    return UY
+
+
+def estep(r2, D, sigma2, gamma, a):
+    """scVectorField.py:197-227.  Returns P (unclamped) and [E, sum P, min nonzero t1, #zeros]."""
+    r2 = dev(r2)
+    N = r2.shape[0]
+    P = empty((N + 2,))
+    stats = empty((4,))
+    _lib.check(lib().dvf_estep(ptr(r2), N, int(D), float(sigma2), float(gamma), float(a), ptr(P), ptr(stats),
+                               stream_ptr()))
+    return P[:N], stats
+
+
+def gram(UY, P, minP, D, M):
+    """scVectorField.py:468-476.  Returns G (ldg x ldg), lower-triangular tiles valid."""
+    UY = dev(UY)
+    N = UY.shape[0]
+    Pp = torch.zeros((N + 2,), dtype=torch.float64, device="cuda")
+    Pp[:N] = dev(P).reshape(-1)
+    ldg = int(lib().dvf_gram_ld(int(D), int(M)))
+    G = torch.zeros((ldg, ldg), dtype=torch.float64, device="cuda")
+    nbytes = C.c_size_t(0)
+    _lib.check(lib().dvf_gram_scratch_bytes(N, int(D), int(M), C.byref(nbytes)))
+    scratch = torch.empty((nbytes.value + 7) // 8, dtype=torch.float64, device="cuda")
+    _lib.check(lib().dvf_gram(ptr(UY), ptr(Pp), float(minP), N, int(D), int(M), ptr(G), ptr(scratch),
+                              nbytes.value, stream_ptr()))
+    return G
+
+
+def solve(G, Kc, M, D, lam_sigma2):
+    """(G[:M,:M] + lam_sigma2 Kc) C = G[M:M+D,:M]^T.   Returns C (M x D), info."""
+    G, Kc = dev(G), dev(Kc)
+    L = empty((M + D, M))
+    Cm = empty((M, D))
+    info = torch.zeros((1,), dtype=torch.int32, device="cuda")
+    _lib.check(lib().dvf_solve(ptr(G), G.shape[1], ptr(Kc), int(M), int(D), float(lam_sigma2), ptr(L), ptr(Cm),
+                               ptr(info), stream_ptr()))
+    return Cm, int(info.item())
+
+
+def update_v(UY, Cm, P, minP, D, M):
+    """scVectorField.py:484-486.  Returns V, r2, sum max(P,minP) r2."""
+    UY, Cm, P = dev(UY), dev(Cm), dev(P).reshape(-1)
+    N = UY.shape[0]
+    V, r2, stats = empty((N, D)), empty((N,)), empty((1,))
+    _lib.check(lib().dvf_update_v(ptr(UY), ptr(Cm), ptr(P), float(minP), N, int(D), int(M), ptr(V), ptr(r2),
+                                  ptr(stats), stream_ptr()))
+    return V, r2, stats

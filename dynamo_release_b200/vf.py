@@ -1,0 +1,226 @@
+"""Host-side mirror of dynamo's vector-field hot-path functions (numpy in -> numpy out, CUDA underneath).
+
+Every public name here has the reference's name, positional order, defaults, return shape / axis order and
+exception types; the arithmetic is done by libdvf_b200 (kernels.py).  Functions the
+reference decorates with @timeit (tools/utils.py:777-798) accept and drop a `timeit=` keyword.
+
+Pass `device_out=True` to keep results on the GPU as torch tensors (benchmark / pipeline mode).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import kernels
+from .device import dev, host
+
+
+def _out(t, device_out):
+    return t if device_out else host(t)
+
+
+def _vf_parts(vf_dict):
+    for key in ("X_ctrl", "beta", "C"):
+        if key not in vf_dict:
+            raise ValueError("vf_dict lacks the key '%s' (need X_ctrl, beta, C)" % key)
+    if vf_dict.get("div_cur_free_kernels", False):
+        raise NotImplementedError("div/curl-free kernels are outside the B200 hot path (Gaussian kernel only)")
+    return vf_dict["X_ctrl"], float(vf_dict["beta"]), vf_dict["C"]
+
+
+def _as2d(x):
+    if isinstance(x, torch.Tensor):
+        return (x[None, :], True) if x.dim() == 1 else (x, False)
+    x = np.asarray(x)
+    return (x[None, :], True) if x.ndim == 1 else (x, False)
+
+
+# ------------------------------------------------------------------------------------------------------
+def con_K(x, y, beta=0.1, method="cdist", return_d=False, timeit=False, device_out=False):
+    """reference vectorfield/utils.py:180-212.  K (n, M), flattened when n == 1 on the values path (:196-197);
+    with return_d also D[n, d, m] = x[n, d] - y[m, d]."""
+    K = kernels.kernel_matrix(x, y, beta)
+    if return_d or method != "cdist":
+        xd, yd = dev(x), dev(y)
+        D = xd[:, :, None] - yd.t()[None, :, :]
+        K = torch.squeeze(K)
+        return (_out(K, device_out), _out(D, device_out)) if return_d else _out(K, device_out)
+    if K.shape[0] == 1:
+        K = K.reshape(-1)
+    return _out(K, device_out)
+
+
+def vector_field_function(x, vf_dict, dim=None, kernel="full", X_ctrl_ind=None, timeit=False, device_out=False,
+                          **kernel_kwargs):
+    """reference vectorfield/utils.py:73-142:  f(x) = K(x, X_ctrl) C."""
+    if kernel not in ("full", "df_kernel", "cf_kernel"):
+        raise ValueError(f"the kernel can only be one of {'full', 'df_kernel', 'cf_kernel'}!")
+    Xc, beta, C = _vf_parts(vf_dict)
+    x2, _ = _as2d(x)
+    if X_ctrl_ind is not None:  # :128-132
+        Cd = dev(C)
+        Cm = torch.zeros_like(Cd)
+        ind = torch.as_tensor(np.asarray(X_ctrl_ind), device=Cd.device)
+        Cm[ind, :] = Cd[ind, :]
+        C = Cm
+    v = kernels.eval_field(x2, Xc, beta, C)
+    if v.shape[0] == 1:
+        v = v.reshape(-1)  # con_K flattens a single row (:196-197), so K.dot(C) is 1-d
+    if dim is not None:
+        v = v[..., :dim] if np.isscalar(dim) else v[..., dim]
+    return _out(v, device_out)
+
+
+class RkhsJacobian:
+    """Callable returned by SvcVectorField.get_Jacobian('analytical'): x -> (D, D, n).  It carries vf_dict so
+    compute_divergence / acceleration / curvature can take the fused no-Jacobian kernel."""
+
+    def __init__(self, vf_dict, **kwargs):
+        self.vf_dict = vf_dict
+        self.kwargs = kwargs
+
+    def __call__(self, x, **kw):
+        return Jacobian_rkhs_gaussian(x, self.vf_dict, **{**self.kwargs, **kw})
+
+
+def Jacobian_rkhs_gaussian(x, vf_dict, vectorize=False, device_out=False):
+    """reference vectorfield/utils.py:351-379.  (D, D, n) for 2-d x, (D, D) for 1-d x."""
+    Xc, beta, C = _vf_parts(vf_dict)
+    x2, single = _as2d(x)
+    J = kernels.jacobian(x2, Xc, beta, C)
+    if single:
+        J = J[:, :, 0]
+    return _out(J, device_out)
+
+
+def Jacobian_rkhs_gaussian_parallel(x, vf_dict, cores=None, device_out=False):
+    """reference vectorfield/utils.py:382-396 (ThreadPool over chunks): one kernel launch here."""
+    return Jacobian_rkhs_gaussian(x, vf_dict, device_out=device_out)
+
+
+# ------------------------------------------------------------------------------------------------------
+# divergence / acceleration / curvature   (reference vectorfield/utils.py:699-821)
+# ------------------------------------------------------------------------------------------------------
+def _fused_ok(vf, f_jac, Js):
+    """The fused no-Jacobian kernel applies when J is not supplied and both callables are this package's
+    RKHS field (same vf_dict)."""
+    if Js is not None or not isinstance(f_jac, RkhsJacobian):
+        return None
+    d = f_jac.vf_dict
+    vd = getattr(vf, "vf_dict", None)
+    if vf is not None and vd is not None and vd is not d:
+        return None
+    if vf is not None and vd is None:
+        return None
+    return d
+
+
+class RkhsField:
+    """Callable x -> f(x) carrying its vf_dict (what SvcVectorField.func is bound to)."""
+
+    def __init__(self, vf_dict):
+        self.vf_dict = vf_dict
+
+    def __call__(self, x, **kw):
+        return vector_field_function(x, self.vf_dict, **kw)
+
+
+def _generic_vJ(vf, f_jac, X, Js):
+    """Generic callables (reference semantics): evaluate them, continue on the device."""
+    v = dev(vf(X)) if vf is not None else None
+    J = dev(f_jac(X) if Js is None else Js)
+    return v, J
+
+
+def compute_divergence(f_jac, X, Js=None, vectorize_size=1000, timeit=False, device_out=False):
+    """reference :699-725.  div_n = tr J_n."""
+    d = _fused_ok(None, f_jac, Js)
+    if d is not None:
+        Xc, beta, C = _vf_parts(d)
+        return _out(kernels.div_acc_curv(X, Xc, beta, C, want=("div",))["div"], device_out)
+    _, J = _generic_vJ(None, f_jac, X, Js)
+    return _out(torch.einsum("iin->n", J), device_out)
+
+
+def compute_acceleration(vf, f_jac, X, Js=None, return_all=False, timeit=False, device_out=False):
+    """reference :770-793.  acce (n,), acce_mat (n, D); with return_all also v (n, D) and J (D, D, n)."""
+    d = _fused_ok(vf, f_jac, Js)
+    if d is not None:
+        Xc, beta, C = _vf_parts(d)
+        r = kernels.div_acc_curv(X, Xc, beta, C, want=("v", "acc", "acc_norm") if return_all else ("acc", "acc_norm"))
+        if return_all:
+            J = kernels.jacobian(X, Xc, beta, C)
+            return _out(r["v"], device_out), _out(J, device_out), _out(r["acc_norm"], device_out), \
+                _out(r["acc"], device_out)
+        return _out(r["acc_norm"], device_out), _out(r["acc"], device_out)
+    v, J = _generic_vJ(vf, f_jac, X, Js)
+    acc = torch.einsum("ijn,nj->ni", J, v)
+    accn = torch.linalg.norm(acc, dim=1)
+    if return_all:
+        return _out(v, device_out), _out(J, device_out), _out(accn, device_out), _out(acc, device_out)
+    return _out(accn, device_out), _out(acc, device_out)
+
+
+def compute_curvature(vf, f_jac, X, Js=None, formula=2, timeit=False, device_out=False):
+    """reference :797-821 with curvature_method2 (:752-757) / curvature_method1 (:743-749)."""
+    d = _fused_ok(vf, f_jac, Js)
+    if d is not None:
+        Xc, beta, C = _vf_parts(d)
+        want = ("curv", "curv_norm") if formula == 2 else ("curv_norm",)
+        r = kernels.div_acc_curv(X, Xc, beta, C, formula=formula, want=want)
+        return _out(r["curv_norm"], device_out), (None if formula != 2 else _out(r["curv"], device_out))
+    v, J = _generic_vJ(vf, f_jac, X, Js)
+    a = torch.einsum("ijn,nj->ni", J, v)
+    vv = (v * v).sum(1)
+    if formula == 1:
+        curv = torch.sqrt(vv * (a * a).sum(1)) / torch.sqrt(vv) ** 3
+        return _out(curv, device_out), None
+    cm = (a * vv[:, None] - v * (v * a).sum(1)[:, None]) / (torch.sqrt(vv) ** 4)[:, None]
+    return _out(torch.linalg.norm(cm, dim=1), device_out), _out(cm, device_out)
+
+
+# ------------------------------------------------------------------------------------------------------
+# PCA -> gene space   (reference vectorfield/utils.py:311-326, 430-554)
+# ------------------------------------------------------------------------------------------------------
+def vector_transformation(V, Q, device_out=False):
+    """reference :311-326:  V Q^T, Q is (genes x PCs)."""
+    Vd = dev(V)
+    single = Vd.dim() == 1
+    out = kernels.vector_transform(Vd[None, :] if single else Vd, Q)
+    return _out(out[0] if single else out, device_out)
+
+
+def elementwise_jacobian_transformation(Js, qi, qj, timeit=False, device_out=False):
+    """reference :430-453:  q_i J_n q_j for every cell, float64 (n,)."""
+    Jd = dev(Js)
+    if Jd.dim() == 2:
+        Jd = Jd[:, :, None]
+    return _out(kernels.gene_transform_elem(Jd.contiguous(), np.asarray(qi).reshape(-1), np.asarray(qj).reshape(-1)),
+                device_out)
+
+
+def transform_jacobian(Js, Qi, Qj, pbar=False, device_out=False):
+    """reference :544-554:  (Ge, Gr, n) float32 = Qi J_n Qj^T."""
+    Jd = dev(Js)
+    if Jd.dim() == 2:
+        Jd = Jd[:, :, None]
+    Qi, Qj = np.atleast_2d(np.asarray(Qi)), np.atleast_2d(np.asarray(Qj))
+    out, _ = kernels.gene_transform(Jd.contiguous(), Qi, Qj)
+    return _out(out, device_out)
+
+
+def subset_jacobian_transformation(Js, Qi, Qj, cores=1, timeit=False, device_out=False):
+    """reference :497-541 (`cores` chunks the cells over a ThreadPool there; one launch here)."""
+    return transform_jacobian(Js, Qi, Qj, device_out=device_out)
+
+
+def average_jacobian_by_group(Js, Qi, Qj, group_labels, n_groups, take_abs=False):
+    """Fused consumer of K8: per-group mean of (|.|) of the float32 gene-space Jacobian, without materialising
+    the (Ge, Gr, n) array -- what rank_jacobian_genes(groups=...) reduces to (rank_vf.py:483-508,
+    utils.py:557-582).  Returns float64 (n_groups, Ge, Gr)."""
+    Jd = dev(Js)
+    lab = np.asarray(group_labels, dtype=np.int32)
+    _, gsum = kernels.gene_transform(Jd.contiguous(), np.atleast_2d(Qi), np.atleast_2d(Qj), take_abs=take_abs,
+                                     group=lab, n_groups=int(n_groups), full=False)
+    cnt = np.bincount(lab, minlength=int(n_groups)).astype(np.float64)
+    return host(gsum) / np.maximum(cnt, 1.0)[:, None, None]

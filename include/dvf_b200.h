@@ -32,6 +32,11 @@ extern "C" {
 int dvf_abi_version(void);
 const char* dvf_last_error(void);
 
+/* Measurement hooks (bench.py): CUDA events around every Gram launch inside dvf_fit_em and a counter of all
+ * kernel launches of the library.  dvf_profile_enable(1) resets both. */
+int dvf_profile_enable(int on);
+int dvf_profile_get(double* gram_ms, int* gram_launches, long long* kernel_launches);
+
 /* K1: K[i, j] = exp(-beta |x_i - Xc_j|^2), row-major n x M with leading dimension ldk (>= M).
  * replaces vectorfield/utils.py:180-212 (con_K, values path). */
 int dvf_kernel_matrix(const double* x, int64_t n, int D, const double* Xc, int M, double beta,

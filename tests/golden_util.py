@@ -1,0 +1,45 @@
+"""Loading of the committed golden vectors (tests/golden/*.npz, written by oracle/gen_golden.py from the
+executed reference).  'lean' cases store a generator recipe + checksums instead of the inputs."""
+import glob
+import os
+
+import numpy as np
+
+from oracle import vfc_oracle
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CASES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(HERE, "golden", "*.npz")))
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+class Golden:
+    def __init__(self, name):
+        self.name = name
+        self.z = np.load(os.path.join(HERE, "golden", name + ".npz"))
+        self.lean = "gen" in self.z.files
+        if self.lean:
+            n, d, seed, vscale = self.z["gen"]
+            X, V = vfc_oracle.hematopoiesis_like(int(n), int(d), seed=int(seed))
+            V = V * vscale
+            cs = np.array([X.sum(), V.sum(), np.abs(X).sum(), np.abs(V).sum()])
+            assert np.allclose(cs, self.z["checksum"], rtol=1e-12), "regenerated inputs differ from the golden recipe"
+            self.X, self.V = X, V
+        else:
+            self.X, self.V = self.z["X"], self.z["V"]
+        self.params = {k: (int(v) if k in ("M", "MaxIter") else float(v))
+                       for k, v in zip(self.z["params_keys"], self.z["params_vals"])}
+        self.stride = 37 if self.lean else 1
+
+    def __getitem__(self, k):
+        return self.z[k]
+
+    def vf(self):
+        return {"X_ctrl": self.z["final_X_ctrl"], "beta": float(self.z["final_beta"]), "C": self.z["final_C"]}
+
+    def floor(self):
+        c, v = float(self.z["floor_relC"]), float(self.z["floor_relV"])
+        return (c if np.isfinite(c) else 0.0), (v if np.isfinite(v) else 0.0)

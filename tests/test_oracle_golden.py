@@ -1,0 +1,53 @@
+"""CPU: the NumPy restatement (oracle/vfc_oracle.py) against the golden vectors produced by executing the
+unmodified reference (oracle/gen_golden.py).  This is what pins the oracle."""
+import numpy as np
+import pytest
+
+from golden_util import CASES, Golden, rel
+from oracle import vfc_oracle as o
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_oracle_fit_matches_reference(name):
+    g = Golden(name)
+    tr = []
+    vf = o.sparse_vfc(g.X, g.V, trace=tr, **g.params)
+    s = g.stride
+    assert vf["iteration"] == int(g["final_iteration"])
+    assert np.array_equal(vf["ctrl_idx"], g["final_ctrl_idx"])
+    assert np.array_equal(vf["X_ctrl"], g["final_X_ctrl"])
+    assert rel(vf["beta"], g["final_beta"]) < 1e-14
+    # same BLAS / LAPACK calls in the same order: identical up to the last bits
+    assert rel(vf["C"], g["final_C"]) < 1e-12
+    assert rel(vf["P"][::s], g["final_P"]) < 1e-12
+    assert rel(vf["sigma2"], g["final_sigma2"]) < 1e-12
+    assert rel(vf["E_traj"], g["final_E_traj"]) < 1e-12
+    assert rel([t["sigma2_in"] for t in tr], g["trace_sigma2_in"]) < 1e-12
+    assert rel(tr[0]["lhs"], g["trace_lhs_0"]) < 1e-13
+    assert rel(tr[1]["rhs"], g["trace_rhs_1"]) < 1e-13
+    full = o.train(g.X, g.V, **g.params)
+    assert rel(full["V"][::s], g["final_Vfit"]) < 1e-12
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_oracle_calculus_matches_reference(name):
+    g = Golden(name)
+    vf = g.vf()
+    xs = g.X[g["calc_cells"]]
+    nj = g["calc_J"].shape[2]
+    assert rel(o.field_eval(xs, vf), g["calc_f"]) < 1e-13
+    assert rel(o.jacobian(xs[:nj], vf), g["calc_J"]) < 1e-13
+    assert rel(o.jacobian(xs[0], vf), g["calc_J_single"]) < 1e-13
+    assert rel(o.divergence(xs, vf), g["calc_div"]) < 1e-13
+    _, _, an, a = o.acceleration(xs, vf)
+    assert rel(an, g["calc_acc"]) < 1e-13 and rel(a, g["calc_acc_mat"]) < 1e-13
+    kn, kv = o.curvature(xs, vf, formula=2)
+    assert rel(kn, g["calc_curv"]) < 1e-12 and rel(kv, g["calc_curv_mat"]) < 1e-12
+    kn1, _ = o.curvature(xs, vf, formula=1)
+    assert rel(kn1, g["calc_curv_f1"]) < 1e-12
+    Q = g["gene_Q"]
+    ng = Q.shape[0]
+    Jg = g["calc_J"][:, :, : g["gene_full"].shape[2]]
+    assert np.array_equal(o.gene_jacobian(Jg, Q[: ng // 2], Q[ng // 3:]), g["gene_full"])
+    assert rel(o.gene_jacobian_element(Jg, Q[1], Q[5]), g["gene_elem"]) < 1e-13
+    assert rel(o.to_gene_space(g["calc_acc_mat"], Q), g["gene_vec"]) < 1e-13
