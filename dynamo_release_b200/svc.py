@@ -95,7 +95,10 @@ class SvcVectorField:
         self.parameters = _update_dict(self.parameters, VecFld)
         self.vf_dict = VecFld
         self.func = _vf.RkhsField(VecFld)
-        self.vf_dict["V"] = self.func(self.data["X"])  # :1043 -- evaluated on ALL rows, overwrites the EM's V
+        # :1043 evaluates f on ALL rows and overwrites the EM's V.  When every row is valid that is the same
+        # product U C the loop just left in V, so it is only recomputed when rows were dropped.
+        if len(VecFld["valid_ind"]) != len(self.data["X"]):
+            self.vf_dict["V"] = self.func(self.data["X"])
         self.vf_dict["normalize"] = self.normalize
         return self.vf_dict
 
