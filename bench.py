@@ -199,16 +199,30 @@ def run_ours(a):
             dist.barrier()
         torch.cuda.synchronize()
 
+    stage_ev = []
+
+    def mark():
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
     def step_device():
         """whole job, inputs resident in HBM, results left in HBM"""
+        ev = [mark()]
         if world > 1:
             st, ctrl, _, beta, _ = fit_sharded(Xd, Vd, M, comm, **em)
+            ev.append(ev[0])
         else:
             _, Xv, Yv, ctrl, _, beta = prelude.run(Xd, Vd, M, seed=0)
+            ev.append(mark())
             st = fit_em(Xv, Yv, ctrl, beta, workspace=state.get("ws"), **em)
             state["ws"] = st.workspace
+        ev.append(mark())
         kernels.jacobian(Xd, ctrl, beta, st.C, out=J_buf)
+        ev.append(mark())
         r = kernels.div_acc_curv(Xd, ctrl, beta, st.C, formula=2)
+        ev.append(mark())
+        stage_ev.append(ev)
         state.update(n_iter=st.n_iter, sigma2=st.sigma2, n_inlier=st.n_inlier, r=r)
 
     def step_e2e():
@@ -228,6 +242,7 @@ def run_ours(a):
     for _ in range(a.warmup):
         step_device()
     lib.dvf_profile_enable(1)
+    stage_ev.clear()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -286,6 +301,8 @@ def run_ours(a):
                              % (N * kernels.row_width(M, D) * 8 / 1e9, J_buf.numel() * 8 / 1e9),
                        "parallelism": "cells sharded over %d GPU(s); Gram/RHS allreduce per EM iteration" % world},
             "clocks": clocks,
+            "stages_ms": {k: float(np.mean([ev[i].elapsed_time(ev[i + 1]) for ev in stage_ev]))
+                          for i, k in enumerate(["prelude", "fit", "jacobian", "div_acc_curv"])},
             "e2e": e2e,
             "gpu_launches": int(launches.value),
             "roofline": {"bound": "tensor", "kernel": "k_gram (weighted Gram + RHS, FP64 DMMA m8n8k4) + k_gram_reduce",

@@ -155,6 +155,7 @@ extern "C" int dvf_fit_em(const double* X, const double* Y, int64_t N, int64_t N
     if (int rc = dvf_kernel_matrix(Xc, M, D, Xc, M, beta, Kc, M, stream)) return rc;
     DVF_CUDA(cudaMemsetAsync(G, 0, sizeof(double) * ((size_t)l.ldg * l.ldg + RED_COUNT), st));
     DVF_CUDA(cudaMemsetAsync(C, 0, sizeof(double) * (size_t)M * D, st));
+    if (int rc = gram_prepare(l.gp, N, D, M, gscratch, st)) return rc;
     k_init_r2<<<l.nblk_es, ES_THREADS, 0, st>>>(UY, N, l.W, M, D, r2, part);
     DVF_LAUNCH_CHECK();
     if (int rc = sum_partials_run(part, l.nblk_es, 1, scal + 3, nullptr, st)) return rc;
