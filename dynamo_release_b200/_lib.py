@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdvf_b200.so")
+LIB_PATH = os.environ.get("DVF_LIB_PATH") or os.path.join(_HERE, "libdvf_b200.so")  # env: developer experiments
 
 DVF_OK, DVF_ERR_ARG, DVF_ERR_CUDA, DVF_ERR_NUMERIC, DVF_ERR_COMM, DVF_ERR_WORKSPACE = 0, -1, -2, -3, -4, -5
 

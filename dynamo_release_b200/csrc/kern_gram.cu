@@ -28,7 +28,15 @@ template <> struct gvar<GV_STRIP4> { static constexpr int RT = 4, CT = 2, WI = 1
 template <> struct gvar<GV_STRIP2> { static constexpr int RT = 2, CT = 2, WI = 1, WJ = 8; };   //  16 x 128
 template <> struct gvar<GV_STRIP1> { static constexpr int RT = 1, CT = 2, WI = 1, WJ = 8; };   //   8 x 128
 // relative cost of one 32-cell step (DMMA count x a penalty for the thinner shapes, measured on B200)
-static const double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.12, 128.0 * 1.15, 64.0 * 1.25, 32.0 * 1.5, 16.0 * 2.2};
+static double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.12, 128.0 * 1.15, 64.0 * 1.25, 32.0 * 1.5, 16.0 * 2.2};
+static int g_force_G = 0;
+static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not part of the ABI
+    static bool done = false;
+    if (done) return;
+    done = true;
+    if (const char* e = getenv("DVF_GRAM_COST")) sscanf(e, "%lf,%lf,%lf,%lf,%lf,%lf", &kVarCost[0], &kVarCost[1], &kVarCost[2], &kVarCost[3], &kVarCost[4], &kVarCost[5]);
+    if (const char* e = getenv("DVF_GRAM_G")) g_force_G = atoi(e);
+}
 
 struct gram_tile { int variant, row0, col0, seg0, nseg; };
 
@@ -109,17 +117,26 @@ __device__ __forceinline__ void gram_segment(const double* __restrict__ UY, cons
             const int row = 4 * k4 + t;
             double p = fmax(ps[row], minP);
             if (n0 + row >= N) p = 0.0;   // rows past the end (zero-filled data, unspecified P)
+#ifdef DVF_EXP_NOSCALE
+            p = 1.0;
+#endif
             double af[RT], bf[CT];
 #pragma unroll
             for (int i = 0; i < RT; ++i) af[i] = a[row * LDA + i * 8];
 #pragma unroll
             for (int j = 0; j < CT; ++j) bf[j] = b[row * LDB + j * 8];
+#ifdef DVF_EXP_NOSCALE
+            if (false) {
+#else
             if (RT <= CT) {
+#endif
 #pragma unroll
                 for (int i = 0; i < RT; ++i) af[i] *= p;
             } else {
+#ifndef DVF_EXP_NOSCALE
 #pragma unroll
                 for (int j = 0; j < CT; ++j) bf[j] *= p;
+#endif
             }
 #pragma unroll
             for (int i = 0; i < RT; ++i)
@@ -207,6 +224,7 @@ struct gram_host_plan {
 };
 
 static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& hp) {
+    read_tuning_env();
     const int units = (M + D + 7) / 8, nfull = units / 16, rt = units % 16;
     auto add = [&](int v, int r0, int c0) { hp.tiles.push_back(gram_tile{v, r0, c0, 0, 0}); };
     for (int s = 0; s < nfull; ++s) {
@@ -250,7 +268,7 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
         if (groups > n_steps) groups = n_steps;
         if (groups < 1) groups = 1;
         const double eff = total / (G * mx) * (double)(G * groups) / n_sms;
-        if (eff > best_eff + 1e-12) { best_eff = eff; best_g = G; best_assign = assign; }
+        if (g_force_G ? (G == g_force_G) : (eff > best_eff + 1e-12)) { best_eff = eff; best_g = G; best_assign = assign; }
     }
     hp.n_groups = (int)std::max<int64_t>(1, std::min<int64_t>(n_sms / best_g, n_steps));
     hp.bundle_off.assign(best_g + 1, 0);

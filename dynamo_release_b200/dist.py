@@ -52,11 +52,15 @@ def gather_rows(t: torch.Tensor, dst: int = 0):
     counts = [torch.zeros_like(n) for _ in range(world)]
     dist.all_gather(counts, n)
     counts = [int(c.item()) for c in counts]
+    # equal-size gather (gloo and nccl both want it): pad every block to the largest row count
+    mx = max(counts) if counts else 0
+    pad = t.contiguous()
+    if t.shape[0] < mx:
+        pad = torch.cat([pad, torch.zeros((mx - t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)], 0)
+    parts = [torch.empty_like(pad) for _ in range(world)] if rank == dst else None
+    dist.gather(pad, parts, dst=dst)
     if rank == dst:
-        parts = [torch.empty((c,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device) for c in counts]
-    else:
-        parts = None
-    dist.gather(t.contiguous(), parts, dst=dst)
+        parts = [p[:c] for p, c in zip(parts, counts)]
     return (torch.cat(parts, 0) if rank == dst else None), counts
 
 

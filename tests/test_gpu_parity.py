@@ -212,3 +212,20 @@ def test_edge_cases(pkg):
         pkg.SvcVectorField(x, x).get_Jacobian("foo")
     with pytest.raises(Exception):
         pkg.SparseVFC(x, np.zeros_like(x) + 1e-9, None, M=3, ecr=2.0)  # loop cannot start: tecr(1) <= ecr
+
+
+def test_sharded_fit_matches_single_gpu():
+    """N-rank NCCL fit == 1-rank fit (runs only where >= 2 GPUs are visible; `gpurun --gpus 2`)."""
+    import os
+    import subprocess
+    import sys
+
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29611", os.path.join(root, "tests", "multi_gpu_check.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    print(out.stdout[-2000:], out.stderr[-2000:])
+    assert out.returncode == 0 and "MULTI_GPU_CHECK PASS" in out.stdout
