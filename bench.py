@@ -60,7 +60,7 @@ def cpu_reference_rate(a, n_iter_full=None, n_fit=50_000, n_eval=1_500):
     from oracle import vfc_oracle as o
     from dynamo_release_b200.datasets import hematopoiesis_like
 
-    X, V = hematopoiesis_like(n_fit, a.pcs, seed=1, velocity_scale=a.velocity_scale)
+    X, V = hematopoiesis_like(n_fit, a.pcs, seed=1, velocity_scale=a.velocity_scale, manifold_seed=7)
     t0 = time.perf_counter()
     vf = o.train(X, V, M=a.ctrl, MaxIter=a.maxiter)
     t_fit = time.perf_counter() - t0
@@ -187,7 +187,7 @@ def run_ours(a):
         comm = Comm()
     lib = _lib.load()
     N, D, M = a.cells, a.pcs, a.ctrl
-    Xh, Vh = hematopoiesis_like(N, D, seed=100 + rank, velocity_scale=a.velocity_scale)
+    Xh, Vh = hematopoiesis_like(N, D, seed=100 + rank, velocity_scale=a.velocity_scale, manifold_seed=7)
     Xh, Vh = pinned_like(Xh), pinned_like(Vh)
     Xd, Vd = torch.from_numpy(Xh).cuda(), torch.from_numpy(Vh).cuda()
     em = dict(MaxIter=a.maxiter)

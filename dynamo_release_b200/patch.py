@@ -1,0 +1,53 @@
+"""install(): rebind dynamo's hot-path names to the B200 implementations.
+
+dynamo looks these functions up by module attribute, and several modules did `from .utils import ...` at import
+time, so every module that holds its own reference is patched (scVectorField.py:38-61, vector_calculus.py:37-48,
+VectorField.py).  `uninstall()` restores the originals.  Nothing is patched unless `dynamo` is importable."""
+from __future__ import annotations
+
+import importlib
+
+from . import svc, vf
+from .sparsevfc import SparseVFC
+
+_NAMES = {
+    "con_K": vf.con_K,
+    "vector_field_function": vf.vector_field_function,
+    "Jacobian_rkhs_gaussian": vf.Jacobian_rkhs_gaussian,
+    "Jacobian_rkhs_gaussian_parallel": vf.Jacobian_rkhs_gaussian_parallel,
+    "compute_divergence": vf.compute_divergence,
+    "compute_acceleration": vf.compute_acceleration,
+    "compute_curvature": vf.compute_curvature,
+    "elementwise_jacobian_transformation": vf.elementwise_jacobian_transformation,
+    "subset_jacobian_transformation": vf.subset_jacobian_transformation,
+    "transform_jacobian": vf.transform_jacobian,
+    "vector_transformation": vf.vector_transformation,
+    "vecfld_from_adata": svc.vecfld_from_adata,
+    "SparseVFC": SparseVFC,
+    "SvcVectorField": svc.SvcVectorField,
+}
+_MODULES = ("dynamo.vectorfield.utils", "dynamo.vectorfield.scVectorField", "dynamo.vectorfield.vector_calculus",
+            "dynamo.vectorfield.VectorField", "dynamo.vectorfield.rank_vf", "dynamo.vectorfield", "dynamo.vf")
+_saved = {}
+
+
+def install(modules=_MODULES):
+    """Returns the list of (module, name) pairs that were rebound."""
+    done = []
+    for modname in modules:
+        try:
+            mod = importlib.import_module(modname)
+        except Exception:
+            continue
+        for name, fn in _NAMES.items():
+            if hasattr(mod, name) and getattr(mod, name) is not fn:
+                _saved[(modname, name)] = getattr(mod, name)
+                setattr(mod, name, fn)
+                done.append((modname, name))
+    return done
+
+
+def uninstall():
+    for (modname, name), orig in list(_saved.items()):
+        setattr(importlib.import_module(modname), name, orig)
+        del _saved[(modname, name)]
