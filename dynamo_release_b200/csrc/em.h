@@ -15,13 +15,14 @@ struct em_ctl {
 enum { RED_SUM_PR2 = 0, RED_SUM_P = 1, RED_SUM_PC = 2, RED_NCORR = 3, RED_COUNT = 8 };
 
 struct gram_plan {
-    int ldg, n_ctas, n_tiles, n_bundles, n_groups;
-    size_t off_tiles, off_boff, off_btiles, off_slots, scratch_bytes;
+    int ldg, n_ctas, n_tiles, n_bundles, n_groups, sb, lag;
+    size_t off_tiles, off_boff, off_btiles, off_progress, off_pclamp, off_slots, scratch_bytes;
 };
 gram_plan make_gram_plan(int64_t N, int D, int M);
 int gram_prepare(const gram_plan& pl, int64_t N, int D, int M, void* scratch, cudaStream_t st);
-int gram_run(const gram_plan& pl, const double* UY, const double* P, double minP, int64_t N, int W, double* G,
-             double* scratch, const int* done, cudaStream_t st);
+// P: already clamped to >= minP
+int gram_run(const gram_plan& pl, const double* UY, const double* P, int64_t N, int W, double* G, double* scratch,
+             const int* done, cudaStream_t st);
 
 int solve_run(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
               const double* lam_sigma2_ptr, double* L, double* C, int* info, const int* done, cudaStream_t st);

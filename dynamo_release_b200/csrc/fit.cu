@@ -179,7 +179,7 @@ extern "C" int dvf_fit_em(const double* X, const double* Y, int64_t N, int64_t N
         if (int rc = trace_run(C, Kc, M, D, part, done, st)) return rc;
         // ---- M-step assembly (:468-476), one allreduce of [G | scalars] ----
         profile_gram_begin(st);
-        if (int rc = gram_run(l.gp, UY, P, prm->minP, N, l.W, G, gscratch, done, st)) return rc;
+        if (int rc = gram_run(l.gp, UY, P, N, l.W, G, gscratch, done, st)) return rc;
         profile_gram_end(st);
         if (int rc = comm_allreduce(comm, G, (int64_t)l.ldg * l.ldg + RED_COUNT, false, st)) return rc;
         k_ctl_energy<<<1, 1, 0, st>>>(ctl, red, part, prm->lambda_, D, E_traj, tecr_traj);

@@ -56,10 +56,10 @@ __global__ void __launch_bounds__(ES_THREADS) k_estep2(const double* __restrict_
         double t1 = P[i];
         if (t1 == 0.0) t1 = tmin;
         const double p = t1 / (t1 + t2);
-        P[i] = p;
         s_pr2 = fma(p, r2[i], s_pr2);
         s_p += p;
         const double pc = fmax(p, minP);
+        P[i] = pc;   // the M-step and everything after it use the clamped posterior (scVectorField.py:468)
         s_pc += pc;
         if (pc > theta) s_nc += 1.0;
     }

@@ -1,83 +1,104 @@
 // K3: weighted Gram + right-hand side of the SparseVFC M-step (reference scVectorField.py:468-476)
-//        G = [U | Y]^T diag(max(P, minP)) [U | Y]      (lower triangle only)
+//        G = [U | Y]^T diag(P) [U | Y]      (lower triangle only; P already clamped to >= minP)
 // so that  lhs = G[:M, :M] + lambda sigma2 Kc   and   rhs[m][d] = G[M + d][m].
 // The reference materialises the M x N temporary U^T * repmat(P) every iteration; here the N x W matrix
 // UY = [U | Y | 0] is built once (K1) and streamed through FP64 tensor cores (DMMA m8n8k4, the contraction
 // index is the cell).  The lower triangle is covered by output tiles of a few shapes (128x128 off the diagonal,
-// 64x64 pieces on it, thin strips for the tail rows) so that little more than the needed triangle is computed;
-// the (tile, cell-range) work space is cut into equal-cost contiguous segments, one run of segments per SM
-// (persistent CTAs, static schedule).  Every segment writes a partial tile; k_gram_reduce sums the partials of a
-// tile in a fixed order, so the result is bitwise reproducible (no atomics).
+// 64x64 pieces on it, 8r x 128 strips for the tail rows) so that little more than the needed triangle is computed.
+//
+// CTA = 16 consumer warps + 1 producer warp.  Four consumer warps per scheduler: a warp can issue a DMMA only
+// every ~17 cycles while the pipe accepts one per 16, so two warps per scheduler cannot also hide their LDS /
+// DMUL issue slots (measured 67% pipe utilisation with 8 warps).  Every consumer warp owns a 32 x 32 block
+// (4 x 4 DMMA tiles, 0.5 LDS per DMMA); tiles smaller than 128 x 128 split the 32 cells of a stage between
+// warps instead of shrinking the warp block (k-split: partials of the k-groups are summed by k_gram_reduce).
+// The producer thread streams 32-cell row blocks of the tile's two column panels into a 3-stage shared-memory
+// ring with TMA (2-D tensor map over UY, box 16 columns x 32 cells, 128-byte swizzle: with the k-step -> row
+// mapping r = 8 (s/2) + 2 t + (s & 1) every fragment load is bank-conflict free), `full` / `empty` mbarriers,
+// no __syncthreads in the loop, and the ring keeps running across tile boundaries.  Rows past N and columns
+// past W are zero-filled by the TMA unit.
+// The CTAs of a group walk the same cells; producers keep within `lag` blocks of the slowest peer (progress
+// words in global memory) so that a row block is fetched from HBM once and served from L2 to the others.
+// Every CTA writes private partial tiles; k_gram_reduce sums them in a fixed order: bitwise reproducible.
 #include <algorithm>
 #include <vector>
+#include <cuda.h>
 #include "em.h"
 
 namespace dvf {
 
-constexpr int GR_KC = 32;        // cells per pipeline stage
+constexpr int GR_KC = 32;            // cells per pipeline stage
 constexpr int GR_STAGES = 3;
-constexpr int GR_SLOT = 128 * 128;   // doubles per partial-tile slot
+constexpr int GR_CWARPS = 16;        // consumer warps
+constexpr int GR_THREADS = (GR_CWARPS + 1) * 32;
+constexpr int GR_SLOT = 128 * 128;   // doubles per partial-tile slot (all k-groups of a tile)
+constexpr int GR_CHUNK_B = 16 * GR_KC * 8;                // bytes of one TMA box: 16 columns x 32 cells
+constexpr int GR_STAGE_B = 16 * GR_CHUNK_B + 1024;        // A panel (8 boxes) + B panel (8 boxes) + P (padded)
+constexpr size_t GR_SMEM = (size_t)GR_STAGES * GR_STAGE_B + 1024 /* alignment slack */ + 64 /* barriers */;
 
-// tile variants: RT x CT DMMA tiles per warp, 8 warps as WI x WJ
-enum { GV_FULL = 0, GV_HALF = 1, GV_STRIP8 = 2, GV_STRIP4 = 3, GV_STRIP2 = 4, GV_STRIP1 = 5, GV_COUNT = 6 };
+// tile variants: every warp owns RT x CT DMMA tiles; 16 warps = WI x WJ positions x KS k-groups
+enum { GV_FULL = 0, GV_HALF = 1, GV_S8 = 2, GV_S4 = 3, GV_S3 = 4, GV_S2 = 5, GV_S1 = 6, GV_COUNT = 7 };
 template <int V> struct gvar;
-template <> struct gvar<GV_FULL>   { static constexpr int RT = 4, CT = 8, WI = 4, WJ = 2; };   // 128 x 128
-template <> struct gvar<GV_HALF>   { static constexpr int RT = 2, CT = 4, WI = 4, WJ = 2; };   //  64 x  64
-template <> struct gvar<GV_STRIP8> { static constexpr int RT = 8, CT = 2, WI = 1, WJ = 8; };   //  64 x 128
-template <> struct gvar<GV_STRIP4> { static constexpr int RT = 4, CT = 2, WI = 1, WJ = 8; };   //  32 x 128
-template <> struct gvar<GV_STRIP2> { static constexpr int RT = 2, CT = 2, WI = 1, WJ = 8; };   //  16 x 128
-template <> struct gvar<GV_STRIP1> { static constexpr int RT = 1, CT = 2, WI = 1, WJ = 8; };   //   8 x 128
-// relative cost of one 32-cell step (DMMA count x a penalty for the thinner shapes, measured on B200)
-static double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.12, 128.0 * 1.15, 64.0 * 1.25, 32.0 * 1.5, 16.0 * 2.2};
-static int g_force_G = 0;
+template <> struct gvar<GV_FULL> { static constexpr int RT = 4, CT = 4, WI = 4, WJ = 4, KS = 1; };   // 128 x 128
+template <> struct gvar<GV_HALF> { static constexpr int RT = 4, CT = 4, WI = 2, WJ = 2, KS = 4; };   //  64 x  64
+template <> struct gvar<GV_S8>   { static constexpr int RT = 4, CT = 4, WI = 2, WJ = 4, KS = 2; };   //  64 x 128
+template <> struct gvar<GV_S4>   { static constexpr int RT = 4, CT = 4, WI = 1, WJ = 4, KS = 4; };   //  32 x 128
+template <> struct gvar<GV_S3>   { static constexpr int RT = 3, CT = 4, WI = 1, WJ = 4, KS = 4; };   //  24 x 128
+template <> struct gvar<GV_S2>   { static constexpr int RT = 2, CT = 4, WI = 1, WJ = 4, KS = 4; };   //  16 x 128
+template <> struct gvar<GV_S1>   { static constexpr int RT = 1, CT = 4, WI = 1, WJ = 4, KS = 4; };   //   8 x 128
+__host__ __device__ inline int gv_rows(int v) {
+    return v == GV_FULL ? 128 : (v == GV_HALF || v == GV_S8) ? 64 : v == GV_S4 ? 32 : v == GV_S3 ? 24 : v == GV_S2 ? 16 : 8;
+}
+__host__ __device__ inline int gv_cols(int v) { return v == GV_HALF ? 64 : 128; }
+__host__ __device__ inline int gv_ks(int v) { return v == GV_FULL ? 1 : v == GV_S8 ? 2 : 4; }
+
+// relative cost of one 32-cell step (DMMA count x a penalty for the smaller shapes, calibrated on B200 with
+// DVF_GRAM_ONLY, tools/gram_tune.py)
+static double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.1, 128.0 * 1.05, 64.0 * 1.1, 48.0 * 1.15, 32.0 * 1.25, 16.0 * 1.6};
+static int g_force_G = 0, g_sb = 64, g_lag = 0, g_only = -1, g_debug = 0;   // sb, lag: measured on B200
 static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not part of the ABI
     static bool done = false;
     if (done) return;
     done = true;
-    if (const char* e = getenv("DVF_GRAM_COST")) sscanf(e, "%lf,%lf,%lf,%lf,%lf,%lf", &kVarCost[0], &kVarCost[1], &kVarCost[2], &kVarCost[3], &kVarCost[4], &kVarCost[5]);
+    if (const char* e = getenv("DVF_GRAM_COST"))
+        sscanf(e, "%lf,%lf,%lf,%lf,%lf,%lf,%lf", &kVarCost[0], &kVarCost[1], &kVarCost[2], &kVarCost[3], &kVarCost[4],
+               &kVarCost[5], &kVarCost[6]);
     if (const char* e = getenv("DVF_GRAM_G")) g_force_G = atoi(e);
+    if (const char* e = getenv("DVF_GRAM_SB")) g_sb = std::max(1, atoi(e));
+    if (const char* e = getenv("DVF_GRAM_LAG")) g_lag = atoi(e);       // blocks a producer may run ahead of its group
+    if (const char* e = getenv("DVF_GRAM_ONLY")) g_only = atoi(e);     // timing experiments: keep one tile variant
+    if (const char* e = getenv("DVF_GRAM_DEBUG")) g_debug = atoi(e);
 }
 
-struct gram_tile { int variant, row0, col0, seg0, nseg; };
+struct gram_tile { int variant, row0, col0, pad0, pad1; };
+struct gr_ring { int stage; unsigned phase; };
+__device__ __forceinline__ void gr_advance(gr_ring& r) { if (++r.stage == GR_STAGES) { r.stage = 0; r.phase ^= 1u; } }
 
-constexpr size_t GR_SMEM = sizeof(double) * (size_t)GR_STAGES * (GR_KC * (132 + 132) + GR_KC);
+// ---- TMA tensor copies (global -> shared, completion on an mbarrier) -------------------------------------
+__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(unsigned dst, const CUtensorMap* map, int c0, unsigned bar) {
+    asm volatile("cp.async.bulk.tensor.1d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2}], [%3];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(bar) : "memory");
+}
 
+// ---- consumer: one tile over `n_steps` ring stages ------------------------------------------------------
+// Swizzled box layout (CU_TENSOR_MAP_SWIZZLE_128B): element (cell r, column cc) of a 16-column box sits at byte
+//   r * 128 + ((cc / 2) ^ (r & 7)) * 16 + (cc & 1) * 8.
+// k-step s of a stage uses the cells r(s, t) = 8 (s / 2) + 2 t + (s & 1), t = 0..3: the 32 lanes of a fragment load
+// (8 columns x 4 cells) then touch every bank exactly twice (2 wavefronts, the minimum for 256 bytes).
 template <int V>
-__device__ __forceinline__ void gram_segment(const double* __restrict__ UY, const double* __restrict__ P, double minP,
-                                             int64_t N, int W, int row0, int col0, int step_lo, int step_hi,
-                                             double* __restrict__ out, bool accumulate, double* smem) {
+__device__ __forceinline__ void gram_consume(int n_steps, double* __restrict__ out, bool accumulate,
+                                             const unsigned char* ring, uint64_t* full, uint64_t* empty, gr_ring& rs) {
     using gv = gvar<V>;
-    constexpr int RT = gv::RT, CT = gv::CT, WI = gv::WI, WJ = gv::WJ;
-    constexpr int TR = 8 * RT * WI, TC = 8 * CT * WJ;
-    constexpr int LDA = TR + ((4 - (TR & 15)) & 15), LDB = TC + ((4 - (TC & 15)) & 15);   // == 4 (mod 16)
-    constexpr int KC = GR_KC, STAGES = GR_STAGES;
-    double* As = smem;                         // [STAGES][KC][LDA]
-    double* Bs = As + STAGES * KC * LDA;       // [STAGES][KC][LDB]
-    double* Ps = Bs + STAGES * KC * LDB;       // [STAGES][KC]
+    constexpr int RT = gv::RT, CT = gv::CT, WJ = gv::WJ, KS = gv::KS;
+    constexpr int TR = 8 * RT * gv::WI, TC = 8 * CT * WJ;
+    constexpr int SPW = (GR_KC / 4) / KS;                 // k-steps per warp and stage (8, 4 or 2)
+    constexpr int POS = gv::WI * WJ;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int wi = warp / WJ, wj = warp % WJ;
-    const int n_steps = step_hi - step_lo;
-    const int64_t n_beg = (int64_t)step_lo * KC;
-
-    auto load_stage = [&](int step, int stage) {
-        const int64_t n0 = n_beg + (int64_t)step * KC;
-        double* a = As + stage * KC * LDA;
-        double* b = Bs + stage * KC * LDB;
-        for (int e = threadIdx.x; e < KC * (TR / 2); e += 256) {
-            const int r = e / (TR / 2), c = 2 * (e % (TR / 2));
-            const bool ok = (n0 + r < N) && (row0 + c < W);
-            cp_async16_zfill(a + r * LDA + c, UY + (ok ? (n0 + r) * (int64_t)W + row0 + c : 0), ok);
-        }
-        for (int e = threadIdx.x; e < KC * (TC / 2); e += 256) {
-            const int r = e / (TC / 2), c = 2 * (e % (TC / 2));
-            const bool ok = (n0 + r < N) && (col0 + c < W);
-            cp_async16_zfill(b + r * LDB + c, UY + (ok ? (n0 + r) * (int64_t)W + col0 + c : 0), ok);
-        }
-        if (threadIdx.x < KC / 2) {
-            const int64_t row = n0 + 2 * threadIdx.x;   // even row, P readable up to an even count (padded)
-            cp_async16_zfill(Ps + stage * KC + 2 * threadIdx.x, P + (row < N ? row : 0), row < N);
-        }
-    };
+    const int kg = warp / POS, pos = warp % POS, wi = pos / WJ, wj = pos % WJ;
+    out += kg * (TR * TC);
 
     double acc[RT][CT][2];
 #pragma unroll
@@ -93,58 +114,48 @@ __device__ __forceinline__ void gram_segment(const double* __restrict__ UY, cons
             }
         }
 
-    __syncthreads();   // the previous segment's readers are done with the ring
+    // per-thread byte offsets inside a box for (s & 1, 8-column half h); RT is even or wi == 0, CT == 4
+    unsigned toff[2][2];
 #pragma unroll
-    for (int st = 0; st < STAGES - 1; ++st) {
-        if (st < n_steps) load_stage(st, st);
-        cp_async_commit();
-    }
+    for (int sp = 0; sp < 2; ++sp)
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            toff[sp][h] = (2 * t + sp) * 128 + ((((h << 2) | (g >> 1)) ^ (2 * t + sp)) << 4) + (g & 1) * 8;
+    // warp bases: A panel box (wi * RT / 2), B panel box (wj * 2), first cell 8 * kg * SPW / 2
+    const unsigned wbase_a = (wi * RT / 2) * GR_CHUNK_B + kg * (SPW / 2) * (8 * 128);
+    const unsigned wbase_b = 8 * GR_CHUNK_B + (wj * 2) * GR_CHUNK_B + kg * (SPW / 2) * (8 * 128);
+    const unsigned wbase_p = 16 * GR_CHUNK_B + (kg * (SPW / 2) * 8 + 2 * t) * 8;
+
     for (int step = 0; step < n_steps; ++step) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        {
-            const int nxt = step + STAGES - 1;
-            if (nxt < n_steps) load_stage(nxt, nxt % STAGES);
-            cp_async_commit();
-        }
-        const int stage = step % STAGES;
-        const double* a = As + stage * KC * LDA + wi * (8 * RT) + g;
-        const double* b = Bs + stage * KC * LDB + wj * (8 * CT) + g;
-        const double* ps = Ps + stage * KC;
-        const int64_t n0 = n_beg + (int64_t)step * KC;
-#pragma unroll (RT * CT >= 32 ? 2 : 8)
-        for (int k4 = 0; k4 < KC / 4; ++k4) {
-            const int row = 4 * k4 + t;
-            double p = fmax(ps[row], minP);
-            if (n0 + row >= N) p = 0.0;   // rows past the end (zero-filled data, unspecified P)
-#ifdef DVF_EXP_NOSCALE
-            p = 1.0;
+        mbar_wait(&full[rs.stage], rs.phase);
+#ifdef DVF_DBG_CONS_SLEEP
+        __nanosleep(DVF_DBG_CONS_SLEEP);
 #endif
+        const unsigned char* sb = ring + rs.stage * GR_STAGE_B;
+#pragma unroll
+        for (int j = 0; j < SPW; ++j) {
+            const int sp = j & 1;
+            const unsigned so = (j >> 1) * (8 * 128);
+            const double p = *reinterpret_cast<const double*>(sb + wbase_p + (j >> 1) * 64 + sp * 8);
             double af[RT], bf[CT];
 #pragma unroll
-            for (int i = 0; i < RT; ++i) af[i] = a[row * LDA + i * 8];
+            for (int i = 0; i < RT; ++i) af[i] = *reinterpret_cast<const double*>(sb + wbase_a + (i >> 1) * GR_CHUNK_B + so + toff[sp][i & 1]);
 #pragma unroll
-            for (int j = 0; j < CT; ++j) bf[j] = b[row * LDB + j * 8];
-#ifdef DVF_EXP_NOSCALE
-            if (false) {
-#else
-            if (RT <= CT) {
-#endif
+            for (int q = 0; q < CT; ++q) bf[q] = *reinterpret_cast<const double*>(sb + wbase_b + (q >> 1) * GR_CHUNK_B + so + toff[sp][q & 1]);
 #pragma unroll
-                for (int i = 0; i < RT; ++i) af[i] *= p;
-            } else {
-#ifndef DVF_EXP_NOSCALE
-#pragma unroll
-                for (int j = 0; j < CT; ++j) bf[j] *= p;
-#endif
-            }
+            for (int i = 0; i < RT; ++i) af[i] *= p;
 #pragma unroll
             for (int i = 0; i < RT; ++i)
 #pragma unroll
-                for (int j = 0; j < CT; ++j) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+                for (int q = 0; q < CT; ++q) dmma(acc[i][q][0], acc[i][q][1], af[i], bf[q]);
         }
+        // generic-proxy reads of this stage must be ordered before the producer's next TMA (async-proxy) write to
+        // it: without the proxy fence the B200 shows stale / torn stages a few times per thousand steps
+        __syncwarp();
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        if (lane == 0) mbar_arrive(&empty[rs.stage]);
+        gr_advance(rs);
     }
-    cp_async_wait<0>();
 #pragma unroll
     for (int i = 0; i < RT; ++i)
 #pragma unroll
@@ -154,66 +165,128 @@ __device__ __forceinline__ void gram_segment(const double* __restrict__ UY, cons
         }
 }
 
-// One CTA = one bundle of tiles (equal total cost across bundles) x one group's cell range.  The G CTAs of a
-// group walk the same cells in the same order at the same pace, so a row block of UY is fetched from HBM once
-// and served to the rest of the group from L2.  A multi-tile bundle round-robins over its tiles in blocks of
-// GR_SB steps, carrying each tile's partial in its private scratch slot.
-constexpr int GR_SB = 32;
-
-template <int V>
-__device__ __forceinline__ void gram_tile_range(const double* UY, const double* P, double minP, int64_t N, int W,
-                                                const gram_tile& tl, int lo, int hi, double* out, bool acc, double* smem) {
-    gram_segment<V>(UY, P, minP, N, W, tl.row0, tl.col0, lo, hi, out, acc, smem);
+// ---- producer (one thread): cells [step*32, step*32+32) of the tile's A (row0..) and B (col0..) panels ------
+__device__ __forceinline__ void gram_produce(const CUtensorMap* mapUY, const CUtensorMap* mapP, const gram_tile& tl, int lo,
+                                             int hi, unsigned char* ring, uint64_t* full, uint64_t* empty, gr_ring& rs) {
+    const int na = (gv_rows(tl.variant) + 15) / 16, nb = gv_cols(tl.variant) / 16;
+    const unsigned bytes = (na + nb) * GR_CHUNK_B + GR_KC * 8;
+    for (int step = lo; step < hi; ++step) {
+        mbar_wait(&empty[rs.stage], rs.phase ^ 1u);
+#ifdef DVF_DBG_PROD_SLEEP
+        __nanosleep(DVF_DBG_PROD_SLEEP);
+#endif
+        const unsigned sb = smem_u32(ring) + rs.stage * GR_STAGE_B, bar = smem_u32(&full[rs.stage]);
+        const int n0 = step * GR_KC;
+        mbar_arrive_expect_tx(&full[rs.stage], bytes);
+        for (int c = 0; c < na; ++c) tma_load_2d(sb + c * GR_CHUNK_B, mapUY, tl.row0 + 16 * c, n0, bar);
+        for (int c = 0; c < nb; ++c) tma_load_2d(sb + (8 + c) * GR_CHUNK_B, mapUY, tl.col0 + 16 * c, n0, bar);
+        tma_load_2d(sb + 16 * GR_CHUNK_B, mapP, n0, 0, bar);
+        gr_advance(rs);
+    }
 }
 
-__global__ void __launch_bounds__(256, 1) k_gram(const double* __restrict__ UY, const double* __restrict__ P, double minP,
-                                                 int64_t N, int W, const gram_tile* __restrict__ tiles, int n_tiles,
-                                                 const int* __restrict__ bundle_off, const int* __restrict__ bundle_tiles,
-                                                 int n_bundles, int n_groups, double* __restrict__ slots,
-                                                 const int* __restrict__ done) {
+// One CTA = one bundle of tiles (equal total cost across bundles) x one group's cell range, walked in blocks of
+// `sb` steps; a multi-tile bundle round-robins over its tiles inside a block, carrying each tile's partial in its
+// private scratch slot.
+__global__ void __launch_bounds__(GR_THREADS, 1) k_gram(const __grid_constant__ CUtensorMap mapUY,
+                                                        const __grid_constant__ CUtensorMap mapP, int64_t N,
+                                                        const gram_tile* __restrict__ tiles, int n_tiles,
+                                                        const int* __restrict__ bundle_off, const int* __restrict__ bundle_tiles,
+                                                        int n_bundles, int n_groups, int sb, int lag, double* __restrict__ slots,
+                                                        int* __restrict__ progress, const int* __restrict__ done) {
     if (done && *done) return;
-    extern __shared__ double smem[];
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    // swizzled TMA boxes need 1024-byte alignment
+    unsigned char* ring = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint64_t* full = reinterpret_cast<uint64_t*>(ring + GR_STAGES * GR_STAGE_B);
+    uint64_t* empty = full + GR_STAGES;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < GR_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], GR_CWARPS); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
     const int grp = blockIdx.x / n_bundles, bun = blockIdx.x % n_bundles;
     const int64_t n_steps = (N + GR_KC - 1) / GR_KC;
     const int s_lo = (int)(n_steps * grp / n_groups), s_hi = (int)(n_steps * (grp + 1) / n_groups);
     const int t_lo = bundle_off[bun], t_hi = bundle_off[bun + 1];
-    const int sb = (t_hi - t_lo == 1) ? (s_hi - s_lo > 0 ? s_hi - s_lo : 1) : GR_SB;
-    bool first = true;
-    for (int b_lo = s_lo; first || b_lo < s_hi; b_lo += sb) {
-        const int b_hi = min(b_lo + sb, s_hi);
-        for (int q = t_lo; q < t_hi; ++q) {
-            const int ti = bundle_tiles[q];
-            const gram_tile tl = tiles[ti];
-            double* out = slots + ((size_t)grp * n_tiles + ti) * GR_SLOT;
-            switch (tl.variant) {
-                case GV_FULL:   gram_tile_range<GV_FULL>(UY, P, minP, N, W, tl, b_lo, b_hi, out, !first, smem); break;
-                case GV_HALF:   gram_tile_range<GV_HALF>(UY, P, minP, N, W, tl, b_lo, b_hi, out, !first, smem); break;
-                case GV_STRIP8: gram_tile_range<GV_STRIP8>(UY, P, minP, N, W, tl, b_lo, b_hi, out, !first, smem); break;
-                case GV_STRIP4: gram_tile_range<GV_STRIP4>(UY, P, minP, N, W, tl, b_lo, b_hi, out, !first, smem); break;
-                case GV_STRIP2: gram_tile_range<GV_STRIP2>(UY, P, minP, N, W, tl, b_lo, b_hi, out, !first, smem); break;
-                default:        gram_tile_range<GV_STRIP1>(UY, P, minP, N, W, tl, b_lo, b_hi, out, !first, smem); break;
+    const int n_blocks = max(1, (s_hi - s_lo + sb - 1) / sb);
+    const bool single = (t_hi - t_lo == 1);
+    gr_ring rs{0, 0u};
+    const int warp = threadIdx.x >> 5;
+
+    if (warp == GR_CWARPS) {
+        // ---------------- producer: one thread ----------------
+        if ((threadIdx.x & 31) != 0) return;
+        int* mine = progress + blockIdx.x;
+        const int* peers = progress + grp * n_bundles;
+        for (int b = 0; b < n_blocks; ++b) {
+            if (n_bundles > 1) {   // stay within `lag` blocks of the slowest CTA of the group (L2 sharing)
+                st_volatile_i32(mine, b + 1);
+                for (int spin = 0; spin < (1 << 16); ++spin) {
+                    int m = 0x7fffffff;
+                    for (int q = 0; q < n_bundles; ++q) m = min(m, ld_volatile_i32(peers + q));
+                    if (m >= b + 1 - lag) break;
+                }
+            }
+            const int b_lo = s_lo + b * sb, b_hi = min(b_lo + sb, s_hi);
+            for (int q = t_lo; q < t_hi; ++q) {
+                const gram_tile tl = tiles[bundle_tiles[q]];
+                gram_produce(&mapUY, &mapP, tl, b_lo, b_hi, ring, full, empty, rs);
             }
         }
-        first = false;
+        if (n_bundles > 1) st_volatile_i32(mine, 0x7ffffff0);   // finished: never hold anyone back
+        return;
+    }
+
+    // ---------------- consumers ----------------
+    auto run = [&](int ti, int n, bool acc) {
+        const gram_tile tl = tiles[ti];
+        double* out = slots + ((size_t)grp * n_tiles + ti) * GR_SLOT;
+        switch (tl.variant) {
+            case GV_FULL: gram_consume<GV_FULL>(n, out, acc, ring, full, empty, rs); break;
+            case GV_HALF: gram_consume<GV_HALF>(n, out, acc, ring, full, empty, rs); break;
+            case GV_S8:   gram_consume<GV_S8>(n, out, acc, ring, full, empty, rs); break;
+            case GV_S4:   gram_consume<GV_S4>(n, out, acc, ring, full, empty, rs); break;
+            case GV_S3:   gram_consume<GV_S3>(n, out, acc, ring, full, empty, rs); break;
+            case GV_S2:   gram_consume<GV_S2>(n, out, acc, ring, full, empty, rs); break;
+            default:      gram_consume<GV_S1>(n, out, acc, ring, full, empty, rs); break;
+        }
+    };
+    if (single) {
+        run(bundle_tiles[t_lo], max(0, s_hi - s_lo), false);
+    } else {
+        for (int b = 0; b < n_blocks; ++b) {
+            const int b_lo = s_lo + b * sb, b_hi = min(b_lo + sb, s_hi);
+            for (int q = t_lo; q < t_hi; ++q) run(bundle_tiles[q], max(0, b_hi - b_lo), b > 0);
+        }
     }
 }
 
-// G[row0 + r][col0 + c] = sum over groups of the tile's partials (fixed order); one CTA column per tile
+// G[row0 + r][col0 + c] = sum over groups and k-groups of the tile's partials (fixed order); one CTA column per
+// tile.  Also rearms the progress words for the next launch.
 __global__ void __launch_bounds__(256) k_gram_reduce(const gram_tile* __restrict__ tiles, int n_tiles, int n_groups,
                                                      const double* __restrict__ slots, double* __restrict__ G, int ldg,
-                                                     const int* __restrict__ done) {
+                                                     int* __restrict__ progress, int n_ctas, const int* __restrict__ done) {
     if (done && *done) return;
+    if (blockIdx.x == 0 && blockIdx.y == 0)
+        for (int i = threadIdx.x; i < n_ctas; i += 256) progress[i] = 0;
     const gram_tile tl = tiles[blockIdx.x];
-    const int TR = (tl.variant == GV_FULL) ? 128 : (tl.variant == GV_HALF || tl.variant == GV_STRIP8) ? 64
-                   : (tl.variant == GV_STRIP4) ? 32 : (tl.variant == GV_STRIP2) ? 16 : 8;
-    const int TC = (tl.variant == GV_HALF) ? 64 : 128;
+    const int TR = gv_rows(tl.variant), TC = gv_cols(tl.variant), KS = gv_ks(tl.variant);
     const double* src = slots + (size_t)blockIdx.x * GR_SLOT;
     for (int e = blockIdx.y * 256 + threadIdx.x; e < TR * TC; e += gridDim.y * 256) {
         double sum = 0.0;
-        for (int gi = 0; gi < n_groups; ++gi) sum += src[(size_t)gi * n_tiles * GR_SLOT + e];
+        for (int gi = 0; gi < n_groups; ++gi)
+            for (int k = 0; k < KS; ++k) sum += src[(size_t)gi * n_tiles * GR_SLOT + k * TR * TC + e];
         const int r = tl.row0 + e / TC, c = tl.col0 + e % TC;
         if (r < ldg && c < ldg) G[(int64_t)r * ldg + c] = sum;
     }
+}
+
+// P clamped to >= minP (step-level entry point; inside dvf_fit_em the E-step stores P already clamped)
+__global__ void k_clamp_copy(const double* __restrict__ P, int64_t N, double minP, double* __restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = fmax(P[i], minP);
 }
 
 // ---- launch plan ---------------------------------------------------------------------------------------
@@ -234,13 +307,18 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
         add(GV_HALF, 128 * s + 64, 128 * s + 64);
     }
     int row = 128 * nfull, rem = rt;
-    const int chunk_units[4] = {8, 4, 2, 1}, chunk_var[4] = {GV_STRIP8, GV_STRIP4, GV_STRIP2, GV_STRIP1};
-    for (int q = 0; q < 4; ++q)
+    const int chunk_units[5] = {8, 4, 3, 2, 1}, chunk_var[5] = {GV_S8, GV_S4, GV_S3, GV_S2, GV_S1};
+    for (int q = 0; q < 5; ++q)
         while (rem >= chunk_units[q]) {
             for (int jb = 0; jb <= nfull; ++jb) add(chunk_var[q], row, 128 * jb);
             row += 8 * chunk_units[q];
             rem -= chunk_units[q];
         }
+    if (g_only >= 0) {
+        std::vector<gram_tile> keep;
+        for (auto& tl : hp.tiles) if (tl.variant == g_only) keep.push_back(tl);
+        if (!keep.empty()) hp.tiles = keep;
+    }
     const int nt = (int)hp.tiles.size();
     const int64_t n_steps = (N + GR_KC - 1) / GR_KC;
     std::vector<int> by_cost(nt);
@@ -255,7 +333,11 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
     double best_eff = -1.0;
     int best_g = 1;
     std::vector<int> best_assign;
-    for (int G = 1; G <= nt && G <= n_sms; ++G) {
+    // bundles no heavier than ~1.25 full tiles: a CTA that owns many tiles re-reads its cells once per tile from
+    // HBM and swaps accumulators at every block, and the group-wise L2 sharing needs several CTAs per group
+    int g_min = (int)(total / (1.25 * kVarCost[GV_FULL]) + 0.5);
+    g_min = std::max(1, std::min(g_min, std::min(nt, n_sms)));
+    for (int G = g_min; G <= nt && G <= n_sms; ++G) {
         std::vector<double> bin(G, 0.0);
         std::vector<int> assign(nt, 0);
         for (int id : by_cost) {
@@ -278,6 +360,13 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
             if (best_assign[i] == k) hp.bundle_tiles.push_back(i);
     }
     hp.bundle_off[best_g] = (int)hp.bundle_tiles.size();
+    if (g_debug) {
+        int cnt[GV_COUNT] = {0};
+        for (auto& tl : hp.tiles) cnt[tl.variant]++;
+        fprintf(stderr, "[gram plan] N=%lld M=%d D=%d tiles=%d (full %d half %d s8 %d s4 %d s3 %d s2 %d s1 %d) bundles=%d groups=%d eff=%.3f\n",
+                (long long)N, M, D, nt, cnt[0], cnt[1], cnt[2], cnt[3], cnt[4], cnt[5], cnt[6], best_g, hp.n_groups, best_eff);
+        g_debug = 0;
+    }
 }
 
 static inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -295,8 +384,12 @@ gram_plan make_gram_plan(int64_t N, int D, int M) {
     pl.off_tiles = o;  o += al256(sizeof(gram_tile) * hp.tiles.size());
     pl.off_boff = o;   o += al256(sizeof(int) * hp.bundle_off.size());
     pl.off_btiles = o; o += al256(sizeof(int) * hp.bundle_tiles.size());
+    pl.off_progress = o; o += al256(sizeof(int) * (size_t)pl.n_ctas);
+    pl.off_pclamp = o; o += al256(sizeof(double) * (size_t)(N + 2));
     pl.off_slots = o;  o += sizeof(double) * (size_t)GR_SLOT * pl.n_tiles * pl.n_groups;
     pl.scratch_bytes = o;
+    pl.sb = g_sb;
+    pl.lag = g_lag;
     return pl;
 }
 
@@ -309,23 +402,71 @@ int gram_prepare(const gram_plan& pl, int64_t N, int D, int M, void* scratch, cu
     DVF_CUDA(cudaMemcpyAsync(base + pl.off_tiles, hp.tiles.data(), sizeof(gram_tile) * hp.tiles.size(), cudaMemcpyHostToDevice, st));
     DVF_CUDA(cudaMemcpyAsync(base + pl.off_boff, hp.bundle_off.data(), sizeof(int) * hp.bundle_off.size(), cudaMemcpyHostToDevice, st));
     DVF_CUDA(cudaMemcpyAsync(base + pl.off_btiles, hp.bundle_tiles.data(), sizeof(int) * hp.bundle_tiles.size(), cudaMemcpyHostToDevice, st));
+    DVF_CUDA(cudaMemsetAsync(base + pl.off_progress, 0, sizeof(int) * (size_t)pl.n_ctas, st));
     return DVF_OK;
 }
 
-int gram_run(const gram_plan& pl, const double* UY, const double* P, double minP, int64_t N, int W, double* G,
-             double* scratch, const int* done, cudaStream_t st) {
+// ---- tensor maps (driver entry point fetched through the runtime: no libcuda link dependency) -----------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_fn get_encode_tiled() {
+    static encode_tiled_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (encode_tiled_fn)p;
+    }
+    return fn;
+}
+
+static int make_maps(const double* UY, const double* P, int64_t N, int W, CUtensorMap* mapUY, CUtensorMap* mapP) {
+    encode_tiled_fn enc = get_encode_tiled();
+    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return DVF_ERR_CUDA; }
+    {
+        const cuuint64_t dims[2] = {(cuuint64_t)W, (cuuint64_t)N}, strides[1] = {(cuuint64_t)W * 8};
+        const cuuint32_t box[2] = {16, GR_KC}, estr[2] = {1, 1};
+        CUresult r = enc(mapUY, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)UY, dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(UY) failed: %d", (int)r); return DVF_ERR_CUDA; }
+    }
+    {
+        // rank 2 with a single row (a rank-1 map is rejected without a stride array)
+        const cuuint64_t dims[2] = {(cuuint64_t)N, 1}, strides[1] = {((cuuint64_t)N * 8 + 15) & ~(cuuint64_t)15};
+        const cuuint32_t box[2] = {GR_KC, 1}, estr[2] = {1, 1};
+        CUresult r = enc(mapP, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)P, dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(P) failed: %d", (int)r); return DVF_ERR_CUDA; }
+    }
+    return DVF_OK;
+}
+
+// P must already be clamped to >= minP (the E-step stores it that way; dvf_gram clamps a copy).
+// UY and P need 16-byte alignment (TMA).
+int gram_run(const gram_plan& pl, const double* UY, const double* P, int64_t N, int W, double* G, double* scratch,
+             const int* done, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
         DVF_CUDA(cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GR_SMEM));
         attr_set = true;
     }
+    DVF_ARG(((uintptr_t)UY & 15) == 0 && ((uintptr_t)P & 15) == 0, "UY and P must be 16-byte aligned");
+    CUtensorMap mapUY, mapP;
+    if (int rc = make_maps(UY, P, N, W, &mapUY, &mapP)) return rc;
     char* base = (char*)scratch;
     const gram_tile* tiles = (const gram_tile*)(base + pl.off_tiles);
     double* slots = (double*)(base + pl.off_slots);
-    k_gram<<<pl.n_ctas, 256, GR_SMEM, st>>>(UY, P, minP, N, W, tiles, pl.n_tiles, (const int*)(base + pl.off_boff),
-                                            (const int*)(base + pl.off_btiles), pl.n_bundles, pl.n_groups, slots, done);
+    int* progress = (int*)(base + pl.off_progress);
+    k_gram<<<pl.n_ctas, GR_THREADS, GR_SMEM, st>>>(mapUY, mapP, N, tiles, pl.n_tiles, (const int*)(base + pl.off_boff),
+                                                  (const int*)(base + pl.off_btiles), pl.n_bundles, pl.n_groups, pl.sb,
+                                                  pl.lag, slots, progress, done);
     DVF_LAUNCH_CHECK();
-    k_gram_reduce<<<dim3(pl.n_tiles, 4), 256, 0, st>>>(tiles, pl.n_tiles, pl.n_groups, slots, G, pl.ldg, done);
+    k_gram_reduce<<<dim3(pl.n_tiles, 4), 256, 0, st>>>(tiles, pl.n_tiles, pl.n_groups, slots, G, pl.ldg, progress,
+                                                      pl.n_ctas, done);
     DVF_LAUNCH_CHECK();
     return DVF_OK;
 }
@@ -353,6 +494,10 @@ extern "C" int dvf_gram(const double* UY, const double* P, double minP, int64_t 
         set_error("gram scratch too small: %zu < %zu", scratch_bytes, pl.scratch_bytes);
         return DVF_ERR_WORKSPACE;
     }
-    if (int rc = gram_prepare(pl, N, D, M, scratch, (cudaStream_t)stream)) return rc;
-    return gram_run(pl, UY, P, minP, N, (int)dvf_fit_row_width(M, D), G, (double*)scratch, nullptr, (cudaStream_t)stream);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (int rc = gram_prepare(pl, N, D, M, scratch, st)) return rc;
+    double* Pc = (double*)((char*)scratch + pl.off_pclamp);
+    k_clamp_copy<<<(unsigned)std::min<int64_t>((N + 255) / 256, 1184), 256, 0, st>>>(P, N, minP, Pc);
+    DVF_LAUNCH_CHECK();
+    return gram_run(pl, UY, Pc, N, (int)dvf_fit_row_width(M, D), G, (double*)scratch, nullptr, st);
 }
