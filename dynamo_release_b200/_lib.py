@@ -61,6 +61,7 @@ SIGNATURES = {
     "dvf_comm_init": (_i, [_p, _i, _i, C.POINTER(_p)]),
     "dvf_comm_destroy": (_i, [_p]),
     "dvf_comm_allreduce_sum": (_i, [_p, _p, _i64, _p]),
+    "dvf_host_cdf": (_i, [_p, _i64, _p]),
 }
 
 _lib = None

@@ -60,5 +60,15 @@ extern "C" int dvf_profile_get(double* gram_ms, int* gram_launches, long long* k
     return DVF_OK;
 }
 
+// numpy.cumsum(p) followed by cdf /= cdf[-1] (Generator.choice, replace=False): one sequential pass + one SIMD pass
+extern "C" int dvf_host_cdf(const double* p, int64_t n, double* cdf) {
+    DVF_ARG(p && cdf && n >= 1, "bad argument");
+    double acc = 0.0;
+    for (int64_t i = 0; i < n; ++i) { acc += p[i]; cdf[i] = acc; }
+    const double tot = cdf[n - 1];
+    for (int64_t i = 0; i < n; ++i) cdf[i] /= tot;
+    return DVF_OK;
+}
+
 extern "C" int dvf_abi_version(void) { return 1; }
 extern "C" const char* dvf_last_error(void) { return dvf::g_err; }

@@ -66,22 +66,55 @@ def unique_rows(X: torch.Tensor):
 
 
 def velocity_weighted_choice(speed: np.ndarray, M: int, seed: int) -> np.ndarray:
-    """tools/sampling.py:242-245 on the host: the random stream is numpy's (Generator.choice)."""
+    """tools/sampling.py:242-245: default_rng(seed).choice(arange(n), size=M, p=speed/sum(speed), replace=False).
+
+    The random stream is numpy's own (Generator.random); the rest restates Generator.choice's replace=False
+    algorithm (numpy/random/_generator.pyx: draw uniforms, cdf = cumsum(p) / cdf[-1], searchsorted(side='right'),
+    keep first occurrences, zero the found entries and repeat) with the O(n) passes fused into one C helper
+    (dvf_host_cdf: the same strictly sequential double-precision accumulation as numpy.cumsum), so the chosen
+    cells are identical -- tests/test_prelude_cpu.py checks it against Generator.choice itself."""
+    from . import _lib
+    import ctypes as C
+    speed = np.ascontiguousarray(speed, dtype=np.float64)
+    n = speed.shape[0]
     rng = np.random.default_rng(seed)
     p = speed / np.sum(speed)
-    return rng.choice(np.arange(len(speed)), size=M, p=p, replace=False)
+    lib = _lib.load()
+    cdf = np.empty(n, dtype=np.float64)
+    found = np.zeros(M, dtype=np.int64)
+    n_uniq = 0
+    while n_uniq < M:
+        x = rng.random((M - n_uniq,))
+        if n_uniq > 0:
+            p[found[0:n_uniq]] = 0
+        _lib.check(lib.dvf_host_cdf(p.ctypes.data_as(C.c_void_p), n, cdf.ctypes.data_as(C.c_void_p)))
+        new = cdf.searchsorted(x, side="right")
+        _, unique_indices = np.unique(new, return_index=True)
+        unique_indices.sort()
+        new = new.take(unique_indices)
+        found[n_uniq:n_uniq + new.size] = new
+        n_uniq += new.size
+    return found
 
 
-def bandwidth(ctrl: np.ndarray) -> float:
+def bandwidth(ctrl) -> float:
     """scVectorField.py:121-135: h = sqrt(2) * mean(dist to the k nearest neighbours) / 1.5,
     k + 1 = max(2, int(0.2 M)).  Exact brute force over the M x M distances (the reference's kd/ball tree is
-    exact too, tools/connectivity.py:565-577)."""
-    n = ctrl.shape[0]
+    exact too, tools/connectivity.py:565-577).  Squared distances are accumulated dimension by dimension with
+    separate multiply / add (the order and rounding sklearn's trees use) on the device `ctrl` lives on; only the
+    M x (k+1) sorted neighbour distances return to the host for NumPy's mean."""
+    c = torch.as_tensor(ctrl, dtype=torch.float64)
+    n = c.shape[0]
     k = max(2, int(0.2 * n)) - 1
-    diff = ctrl[:, None, :] - ctrl[None, :, :]
-    dist = np.sqrt(np.einsum("ijk,ijk->ij", diff, diff))
+    ct = c.T.contiguous()
+    d2 = torch.zeros((n, n), dtype=torch.float64, device=c.device)
+    diff = torch.empty_like(d2)
+    for d in range(ct.shape[0]):
+        torch.sub(ct[d][:, None], ct[d][None, :], out=diff)
+        torch.mul(diff, diff, out=diff)
+        d2 += diff
     kk = min(k + 1, n)
-    part = np.sort(np.partition(dist, kk - 1, axis=1)[:, :kk], axis=1)
+    part = torch.sqrt(torch.topk(d2, kk, dim=1, largest=False, sorted=True).values).cpu().numpy()
     return float(np.sqrt(2) * (np.mean(part[:, 1:]) / 1.5))
 
 
@@ -99,8 +132,9 @@ def run(X: torch.Tensor, Y: torch.Tensor, M: int, seed: int = 0, beta=None, velo
         idx = velocity_weighted_choice(speed, M, seed)
     else:
         idx = np.random.RandomState(seed=seed).permutation(n_u)[:M]  # scVectorField.py:409-410
-    ctrl = uniq[torch.as_tensor(idx, device=X.device)].cpu().numpy()
+    ctrl_t = uniq[torch.as_tensor(idx, device=X.device)]
+    ctrl = ctrl_t.cpu().numpy()
     if beta is None:
-        h = bandwidth(ctrl)
+        h = bandwidth(ctrl_t)
         beta = 1.0 / h**2
     return valid, Xv, Yv, ctrl, idx, float(beta)

@@ -36,7 +36,7 @@ class SvcVectorField:
     """Same constructor, attributes (`data`, `vf_dict`, `func`, `parameters`, `norm_dict`, `normalize`) and
     methods as the reference class."""
 
-    def __init__(self, X=None, V=None, Grid=None, normalize=False, **kwargs):
+    def __init__(self, X=None, V=None, Grid=None, normalize=None, *args, **kwargs):
         self.data = {"X": X, "V": V, "Grid": Grid}
         self.vf_dict = kwargs.pop("vf_dict", {})
         self.func = kwargs.pop("func", None)

@@ -149,6 +149,12 @@ int dvf_comm_init(const void* id128, int rank, int world, void** comm);
 int dvf_comm_destroy(void* comm);
 int dvf_comm_allreduce_sum(void* comm, double* buf, int64_t count, void* stream);
 
+/* ---- host helper of the prelude -------------------------------------------------------------------------
+ * Control-point sampling (reference tools/sampling.py:242-245 -> numpy Generator.choice(p=..., replace=False)):
+ * cdf[i] = (p[0] + ... + p[i]) / total, accumulated strictly left to right in double precision exactly as
+ * numpy.cumsum does, so that searchsorted() picks the same cells as the reference.  HOST pointers, no CUDA. */
+int dvf_host_cdf(const double* p, int64_t n, double* cdf);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,60 @@
+"""patch.install() against the UNMODIFIED reference modules (loaded from /root/reference under import stubs):
+every hot-path name is rebound in every module that holds a reference, and each replacement accepts the reference's
+parameter names, order and defaults.  Skipped where the reference tree is absent (GPU box)."""
+import inspect
+
+import pytest
+
+from oracle import ref_loader
+
+pytestmark = pytest.mark.skipif(not ref_loader.available(), reason="reference tree not present")
+
+
+@pytest.fixture(scope="module")
+def ref_modules():
+    ref_loader.install()
+    mods = {m: ref_loader.load(m) for m in ("dynamo.vectorfield.utils", "dynamo.vectorfield.scVectorField",
+                                            "dynamo.vectorfield.vector_calculus", "dynamo.vectorfield.VectorField",
+                                            "dynamo.vectorfield.rank_vf")}
+    return mods
+
+
+def _params(fn):
+    fn = inspect.unwrap(fn)
+    return [(p.name, p.default) for p in inspect.signature(fn).parameters.values()
+            if p.kind in (p.POSITIONAL_ONLY, p.POSITIONAL_OR_KEYWORD)]
+
+
+def test_signatures_match_the_reference(ref_modules):
+    from dynamo_release_b200 import patch
+    utils, scvf = ref_modules["dynamo.vectorfield.utils"], ref_modules["dynamo.vectorfield.scVectorField"]
+    for name, ours in patch._NAMES.items():
+        ref = getattr(utils, name, None) or getattr(scvf, name, None)
+        assert ref is not None, name
+        if inspect.isclass(ref):
+            ref, ours = ref.__init__, ours.__init__
+        rp, op = _params(ref), _params(ours)
+        # same leading parameters in the same order with the same defaults; ours may add keyword-only extras
+        assert [n for n, _ in op[:len(rp)]] == [n for n, _ in rp], (name, rp, op)
+        for (n, rd), (_, od) in zip(rp, op):
+            if rd is inspect.Parameter.empty:
+                assert od is inspect.Parameter.empty, (name, n)
+            else:
+                assert od == rd or (od is None and rd is None), (name, n, rd, od)
+
+
+def test_install_rebinds_every_holder_and_uninstall_restores(ref_modules):
+    from dynamo_release_b200 import patch
+    before = {(m, n): getattr(mod, n) for m, mod in ref_modules.items() for n in patch._NAMES if hasattr(mod, n)}
+    done = patch.install(modules=tuple(ref_modules))
+    try:
+        assert set(done) == set(before), set(before) ^ set(done)
+        for (m, n) in before:
+            assert getattr(ref_modules[m], n) is patch._NAMES[n]
+        # the modules that imported the names with `from .utils import ...` hold their own references
+        assert ("dynamo.vectorfield.vector_calculus", "Jacobian_rkhs_gaussian") in before or \
+               ("dynamo.vectorfield.scVectorField", "Jacobian_rkhs_gaussian") in before
+    finally:
+        patch.uninstall()
+    for (m, n), fn in before.items():
+        assert getattr(ref_modules[m], n) is fn

@@ -45,3 +45,13 @@ def test_bandwidth_matches_sklearn_tree():
     for shape in [(100, 30), (64, 2), (7, 3), (2, 5)]:
         c = rng.normal(size=shape)
         assert abs(prelude.bandwidth(c) - o.knn_bandwidth(c)) <= 1e-14 * o.knn_bandwidth(c)
+
+
+def test_velocity_weighted_choice_equals_numpy_generator_choice():
+    """The restated replace=False algorithm (C cumsum helper) picks exactly the cells Generator.choice picks."""
+    for trial, (n, M) in enumerate([(200000, 500), (1000, 100), (300, 300), (50, 7), (5000, 100), (200, 199)]):
+        rng = np.random.default_rng(trial)
+        speed = np.abs(rng.normal(size=n)) + (0.0 if trial % 2 else 1e-3)
+        for seed in (0, 1, 19491001):
+            ref = np.random.default_rng(seed).choice(np.arange(n), size=M, p=speed / np.sum(speed), replace=False)
+            assert np.array_equal(ref, prelude.velocity_weighted_choice(speed, M, seed)), (n, M, seed)
