@@ -1,5 +1,6 @@
 // Error plumbing and ABI version of libdvf_b200.
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace dvf {
 static thread_local char g_err[512] = "";
@@ -15,6 +16,46 @@ int cuda_fail(cudaError_t e, const char* what, int line) {
     return DVF_ERR_CUDA;
 }
 long long g_launch_count = 0;
+
+// ---- tensor maps ---------------------------------------------------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static encode_tiled_fn get_encode_tiled() {
+    static encode_tiled_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (encode_tiled_fn)p;
+    }
+    return fn;
+}
+static int encode_2d(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, uint64_t pitch, uint32_t bc,
+                     uint32_t br, CUtensorMapSwizzle sw, CUtensorMapL2promotion l2) {
+    encode_tiled_fn enc = get_encode_tiled();
+    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return DVF_ERR_CUDA; }
+    if (((uintptr_t)base & 15) != 0 || (pitch & 15) != 0) {
+        set_error("TMA source needs a 16-byte aligned base and row pitch");
+        return DVF_ERR_ARG;
+    }
+    const cuuint64_t dims[2] = {cols, rows}, strides[1] = {pitch};
+    const cuuint32_t box[2] = {bc, br}, estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, sw, l2, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed: %d", (int)r); return DVF_ERR_CUDA; }
+    return DVF_OK;
+}
+int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, uint64_t pitch_bytes) {
+    return encode_2d(map, base, cols, rows, pitch_bytes, TMA_BOX_COLS, TMA_BOX_ROWS, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+}
+int make_tmap_vec(CUtensorMap* map, const void* base, uint64_t n) {
+    // rank 2 with a single row (a rank-1 map is rejected without a stride array)
+    return encode_2d(map, base, n, 1, (n * 8 + 15) & ~(uint64_t)15, 32, 1, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_NONE);
+}
 
 // ---- CUDA-event profile of the Gram launches (the dominant kernel) -----------------------------------
 static bool g_prof_on = false;

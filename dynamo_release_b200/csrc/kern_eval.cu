@@ -58,8 +58,8 @@ __global__ void __launch_bounds__(256) k_kernel_matrix(const double* __restrict_
             }
         }
     }
-    // fused [U | Y | 0]: copy Y and zero the padding columns (only when building the fit matrix)
-    if (Y != nullptr) {
+    // fused [U | Y | 0]: copy Y (if any) and zero the padding columns
+    if (ycols + padcols > 0) {
         const int extra = ycols + padcols;
         for (int e = threadIdx.x; e < K1_T * extra; e += 256) {
             int r = e / extra, c = e % extra;
@@ -249,6 +249,17 @@ extern "C" int dvf_kernel_matrix(const double* x, int64_t n, int D, const double
     if (n == 0) return DVF_OK;
     k_kernel_matrix<<<(unsigned)((n + K1_T - 1) / K1_T), 256, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, K, ldk,
                                                                                        nullptr, 0, 0);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}
+
+// K with the columns M .. ldk-1 zero-filled (operand of the Jacobian GEMM; internal)
+extern "C" int dvf_kernel_matrix_padded(const double* x, int64_t n, int D, const double* Xc, int M, double beta, double* K,
+                                        int64_t ldk, void* stream) {
+    DVF_ARG(n >= 0 && M >= 1 && D >= 1 && ldk >= M && K && Xc, "bad argument");
+    if (n == 0) return DVF_OK;
+    k_kernel_matrix<<<(unsigned)((n + K1_T - 1) / K1_T), 256, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, K, ldk,
+                                                                                       nullptr, 0, (int)(ldk - M));
     DVF_LAUNCH_CHECK();
     return DVF_OK;
 }

@@ -21,8 +21,8 @@
 // Every CTA writes private partial tiles; k_gram_reduce sums them in a fixed order: bitwise reproducible.
 #include <algorithm>
 #include <vector>
-#include <cuda.h>
 #include "em.h"
+#include "tma.cuh"
 
 namespace dvf {
 
@@ -72,16 +72,6 @@ static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not p
 struct gram_tile { int variant, row0, col0, pad0, pad1; };
 struct gr_ring { int stage; unsigned phase; };
 __device__ __forceinline__ void gr_advance(gr_ring& r) { if (++r.stage == GR_STAGES) { r.stage = 0; r.phase ^= 1u; } }
-
-// ---- TMA tensor copies (global -> shared, completion on an mbarrier) -------------------------------------
-__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void tma_load_1d(unsigned dst, const CUtensorMap* map, int c0, unsigned bar) {
-    asm volatile("cp.async.bulk.tensor.1d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2}], [%3];"
-                 ::"r"(dst), "l"(map), "r"(c0), "r"(bar) : "memory");
-}
 
 // ---- consumer: one tile over `n_steps` ring stages ------------------------------------------------------
 // Swizzled box layout (CU_TENSOR_MAP_SWIZZLE_128B): element (cell r, column cc) of a 16-column box sits at byte
@@ -152,7 +142,7 @@ __device__ __forceinline__ void gram_consume(int n_steps, double* __restrict__ o
         // generic-proxy reads of this stage must be ordered before the producer's next TMA (async-proxy) write to
         // it: without the proxy fence the B200 shows stale / torn stages a few times per thousand steps
         __syncwarp();
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        fence_proxy_async_smem();
         if (lane == 0) mbar_arrive(&empty[rs.stage]);
         gr_advance(rs);
     }
@@ -406,45 +396,6 @@ int gram_prepare(const gram_plan& pl, int64_t N, int D, int M, void* scratch, cu
     return DVF_OK;
 }
 
-// ---- tensor maps (driver entry point fetched through the runtime: no libcuda link dependency) -----------
-typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static encode_tiled_fn get_encode_tiled() {
-    static encode_tiled_fn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = (encode_tiled_fn)p;
-    }
-    return fn;
-}
-
-static int make_maps(const double* UY, const double* P, int64_t N, int W, CUtensorMap* mapUY, CUtensorMap* mapP) {
-    encode_tiled_fn enc = get_encode_tiled();
-    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return DVF_ERR_CUDA; }
-    {
-        const cuuint64_t dims[2] = {(cuuint64_t)W, (cuuint64_t)N}, strides[1] = {(cuuint64_t)W * 8};
-        const cuuint32_t box[2] = {16, GR_KC}, estr[2] = {1, 1};
-        CUresult r = enc(mapUY, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)UY, dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(UY) failed: %d", (int)r); return DVF_ERR_CUDA; }
-    }
-    {
-        // rank 2 with a single row (a rank-1 map is rejected without a stride array)
-        const cuuint64_t dims[2] = {(cuuint64_t)N, 1}, strides[1] = {((cuuint64_t)N * 8 + 15) & ~(cuuint64_t)15};
-        const cuuint32_t box[2] = {GR_KC, 1}, estr[2] = {1, 1};
-        CUresult r = enc(mapP, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)P, dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled(P) failed: %d", (int)r); return DVF_ERR_CUDA; }
-    }
-    return DVF_OK;
-}
-
 // P must already be clamped to >= minP (the E-step stores it that way; dvf_gram clamps a copy).
 // UY and P need 16-byte alignment (TMA).
 int gram_run(const gram_plan& pl, const double* UY, const double* P, int64_t N, int W, double* G, double* scratch,
@@ -456,7 +407,8 @@ int gram_run(const gram_plan& pl, const double* UY, const double* P, int64_t N, 
     }
     DVF_ARG(((uintptr_t)UY & 15) == 0 && ((uintptr_t)P & 15) == 0, "UY and P must be 16-byte aligned");
     CUtensorMap mapUY, mapP;
-    if (int rc = make_maps(UY, P, N, W, &mapUY, &mapP)) return rc;
+    if (int rc = make_tmap_2d(&mapUY, UY, (uint64_t)W, (uint64_t)N, (uint64_t)W * 8)) return rc;
+    if (int rc = make_tmap_vec(&mapP, P, (uint64_t)N)) return rc;
     char* base = (char*)scratch;
     const gram_tile* tiles = (const gram_tile*)(base + pl.off_tiles);
     double* slots = (double*)(base + pl.off_slots);

@@ -1,153 +1,197 @@
-// K6: per-cell analytical Jacobian of the Gaussian-RKHS field, direct form (reference utils.py:351-379)
+// K6: per-cell analytical Jacobian of the Gaussian-RKHS field (reference utils.py:351-379)
 //     J_c[i][j] = -2 beta sum_m k(x_c, Xc_m) C[m][i] (x_c[j] - Xc[m][j])
-// computed as one small FP64 tensor-core GEMM per cell:  J_c = A_c^T B_c  with
-//     A_c[m][i] = k_cm C[m][i]      B_c[m][j] = x_c[j] - Xc[m][j]
-// Both operands are generated in registers straight into DMMA m8n8k4 fragments (one DMUL / DADD per fragment
-// element, 2/D of the MMA work); the D x D accumulators of a cell live in the registers of one warp; K is
-// never materialised.  Control points / coefficients are staged through shared memory in chunks of 64.
+// written as ONE dense FP64 tensor-core GEMM over all cells.  With any fixed shift s (the centroid of the
+// control points, which keeps the two terms small),
+//     sum_m k_cm C_mi (x_cj - c_mj) = v_ci (x_cj - s_j) - sum_m k_cm T[m][(i, j)],   T[m][(i, j)] = C_mi (c_mj - s_j),
+//     v_ci = sum_m k_cm C_mi,
+// so the (D*D) x n matrix J is (T_ext)^T (M x rows) times K^T (M x n) plus a rank-one correction per cell; the rows
+// that produce v_i are appended to the row tile that needs them, so one pass over K gives both.
+// The output layout (D, D, n), cell index fastest, is the reference's (utils.py:368) and is exactly the row-major
+// GEMM result: every row of 128 cells is a contiguous 1 KB run.
+//   pre-pass : K = exp(-beta |x - c|^2) for a chunk of cells (k_kernel_matrix, direct distance form like cdist)
+//   GEMM     : persistent CTAs, 16 consumer warps (32 x 32 block each, 128 rows x 128 cells per item) + 1 TMA producer
+//              thread, 3-stage ring of 32 control points, 128-byte swizzled boxes; the k-step -> control-point mapping
+//              m(s, t) = 8 (s/2) + 2 (s&1) + (t&1) + 4 (t/2) makes both the A loads (control point = box row) and the
+//              B loads (control point = box column) bank-conflict free.
+// The direct per-cell form (kern_jacobian_direct.cu) is kept for cross-checks: DVF_JAC_DIRECT=1.
+#include <cstdlib>
 #include "common.cuh"
+#include "tma.cuh"
+
+int dvf_jacobian_direct_impl(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                             double* J, void* stream);
+extern "C" int dvf_kernel_matrix_padded(const double* x, int64_t n, int D, const double* Xc, int M, double beta, double* K,
+                                        int64_t ldk, void* stream);
 
 namespace dvf {
 
-constexpr int JC_MC = 64;        // ctrl points per chunk
-constexpr int JC_WARPS = 8;
+constexpr int JG_STAGES = 3;
+constexpr int JG_CWARPS = 16;
+constexpr int JG_THREADS = (JG_CWARPS + 1) * 32;
+constexpr int JG_KC = 32;                                   // control points per stage
+constexpr int JG_STAGE_B = 16 * TMA_BOX_BYTES;              // A panel: 8 boxes (128 rows), B panel: 8 boxes (128 cells)
+constexpr int JG_VROWS = 12;                                // v rows a tile can hold (n_i <= 11 for D >= 10, <= D below)
+constexpr size_t JG_SMEM = (size_t)JG_STAGES * JG_STAGE_B + JG_VROWS * 128 * 8 + 1024 + 64;
+constexpr int64_t JG_CHUNK = 131072;                        // cells per K chunk (0.5 GB at M = 500)
 
-template <int NT>
-struct jac_cfg {
-    static constexpr int DP = NT * 8;
-    static constexpr int CPW = (NT <= 4) ? 2 : 1;            // cells per warp
-    static constexpr int SPLIT = (NT >= 7) ? 2 : 1;          // warps sharing one cell (row halves of J)
-    static constexpr int NTI = (SPLIT == 2) ? (NT + 1) / 2 : NT;   // row tiles owned by a warp
-    static constexpr int CELLS = JC_WARPS * CPW / SPLIT;     // cells per CTA
-    static constexpr int LDC = ((DP + 15) / 16) * 16 + 4;    // == 4 (mod 16): conflict-free fragment loads
-    static constexpr int LDT = JC_MC + 1;                    // transposed ctrl tile, lane = ctrl point
-    static constexpr size_t SMEM = sizeof(double) * (size_t)(2 * JC_MC * LDC + DP * LDT + CELLS * DP);
-};
+struct jg_ring { int stage; unsigned phase; };
+__device__ __forceinline__ void jg_advance(jg_ring& r) { if (++r.stage == JG_STAGES) { r.stage = 0; r.phase ^= 1u; } }
 
-template <int NT>
-__global__ void __launch_bounds__(JC_WARPS * 32) k_jacobian(const double* __restrict__ x, int64_t n, int D,
-                                                            const double* __restrict__ Xc, int M, double beta,
-                                                            const double* __restrict__ C, double* __restrict__ J) {
-    using cfg = jac_cfg<NT>;
-    constexpr int DP = cfg::DP, CPW = cfg::CPW, LDC = cfg::LDC, LDT = cfg::LDT, NTI = cfg::NTI;
-    extern __shared__ double smem[];
-    double* cs = smem;                     // [MC][LDC]  ctrl points, row-major (B fragments)
-    double* Cs = cs + JC_MC * LDC;         // [MC][LDC]  coefficients, row-major (A fragments)
-    double* cT = Cs + JC_MC * LDC;         // [DP][LDT]  ctrl points transposed (distance phase)
-    double* xs = cT + DP * LDT;            // [CELLS][DP] this CTA's cells
+// rows of tile t: group gl = r / (D+1) -> i = t * n_i + gl, e = r % (D+1): e < D is the (i, j=e) entry, e == D is v_i
+__host__ __device__ inline int jg_ni(int D) { int n = 128 / (D + 1); return n > D ? D : n; }
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int64_t cell0 = (int64_t)blockIdx.x * cfg::CELLS;
-    const int wcell = (cfg::SPLIT == 2) ? (warp >> 1) : warp * CPW;   // first local cell of this warp
-    const int ib0 = (cfg::SPLIT == 2) ? (warp & 1) * NTI : 0;         // first row tile of this warp
+// s[d] = mean_m Xc[m][d]  (any shift is algebraically exact; the centroid keeps |c - s| small)
+__global__ void k_jg_centroid(const double* __restrict__ Xc, int M, int D, double* __restrict__ s) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= D) return;
+    double a = 0.0;
+    for (int m = 0; m < M; ++m) a += Xc[(int64_t)m * D + d];
+    s[d] = a / M;
+}
 
-    for (int e = threadIdx.x; e < cfg::CELLS * DP; e += blockDim.x) {
-        int r = e / DP, d = e % DP;
-        int64_t c = cell0 + r;
-        xs[e] = (c < n && d < D) ? x[c * D + d] : 0.0;
-    }
-    __syncthreads();
-
-    double acc[CPW][NTI][NT][2];
-    double xg[CPW][NT];
-#pragma unroll
-    for (int c = 0; c < CPW; ++c) {
-#pragma unroll
-        for (int jb = 0; jb < NT; ++jb) xg[c][jb] = xs[(wcell + c) * DP + jb * 8 + g];
-#pragma unroll
-        for (int ib = 0; ib < NTI; ++ib)
-#pragma unroll
-            for (int jb = 0; jb < NT; ++jb) acc[c][ib][jb][0] = acc[c][ib][jb][1] = 0.0;
-    }
-
-    for (int m0 = 0; m0 < M; m0 += JC_MC) {
-        __syncthreads();
-        for (int e = threadIdx.x; e < JC_MC * DP; e += blockDim.x) {
-            int r = e / DP, d = e % DP;
-            bool ok = (m0 + r < M) && d < D;
-            double cv = ok ? Xc[(int64_t)(m0 + r) * D + d] : 0.0;
-            cs[r * LDC + d] = cv;
-            cT[d * LDT + r] = cv;
-            Cs[r * LDC + d] = ok ? C[(int64_t)(m0 + r) * D + d] : 0.0;
-        }
-        __syncthreads();
-
-        // distance phase: lane = ctrl point, two rounds of 32
-        double kk[CPW][JC_MC / 32];
-#pragma unroll
-        for (int c = 0; c < CPW; ++c) {
-            const double* xc = xs + (wcell + c) * DP;
-#pragma unroll
-            for (int r = 0; r < JC_MC / 32; ++r) {
-                double d2 = 0.0;
-#pragma unroll 8
-                for (int d = 0; d < DP; ++d) {
-                    double tt = xc[d] - cT[d * LDT + r * 32 + lane];
-                    d2 = fma(tt, tt, d2);
-                }
-                kk[c][r] = (m0 + r * 32 + lane < M) ? exp(-beta * d2) : 0.0;
-            }
-        }
-
-        // MMA phase: k-steps of 4 ctrl points
-#pragma unroll 2
-        for (int s = 0; s < JC_MC / 4; ++s) {
-            const int row = 4 * s + t;
-            double cfrag[NT], Cfrag[NTI];
-#pragma unroll
-            for (int b = 0; b < NT; ++b) cfrag[b] = cs[row * LDC + b * 8 + g];
-#pragma unroll
-            for (int b = 0; b < NTI; ++b) Cfrag[b] = (ib0 + b < NT) ? Cs[row * LDC + (ib0 + b) * 8 + g] : 0.0;
-#pragma unroll
-            for (int c = 0; c < CPW; ++c) {
-                const double kv = __shfl_sync(0xffffffffu, (s < 8) ? kk[c][0] : kk[c][1], ((4 * s) & 31) + t);
-                double a[NTI], b[NT];
-#pragma unroll
-                for (int q = 0; q < NTI; ++q) a[q] = kv * Cfrag[q];
-#pragma unroll
-                for (int q = 0; q < NT; ++q) b[q] = xg[c][q] - cfrag[q];
-#pragma unroll
-                for (int ib = 0; ib < NTI; ++ib)
-                    if (cfg::SPLIT == 1 || ib0 + ib < NT) {
-#pragma unroll
-                        for (int jb = 0; jb < NT; ++jb) dmma(acc[c][ib][jb][0], acc[c][ib][jb][1], a[ib], b[jb]);
-                    }
-            }
-        }
-    }
-
-    // epilogue: J[(i*D + j)*n + cell] (cell index fastest, reference layout (D, D, n))
-    const double sc = -2.0 * beta;
-#pragma unroll
-    for (int c = 0; c < CPW; ++c) {
-        const int64_t cell = cell0 + wcell + c;
-        if (cell >= n) continue;
-#pragma unroll
-        for (int ib = 0; ib < NTI; ++ib)
-#pragma unroll
-            for (int jb = 0; jb < NT; ++jb) {
-                const int i = (ib0 + ib) * 8 + g, j = jb * 8 + 2 * t;
-                if (i < D) {
-                    if (j < D) J[((int64_t)i * D + j) * n + cell] = sc * acc[c][ib][jb][0];
-                    if (j + 1 < D) J[((int64_t)i * D + j + 1) * n + cell] = sc * acc[c][ib][jb][1];
-                }
-            }
+// T_ext[m][t * 128 + r] for m < Mp (zero rows past M), zero for the padding rows of a tile
+__global__ void k_jg_build_t(const double* __restrict__ Xc, const double* __restrict__ C, const double* __restrict__ s,
+                             int M, int Mp, int D, int n_tiles, double* __restrict__ T) {
+    const int ncols = n_tiles * 128, n_i = jg_ni(D);
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < (int64_t)Mp * ncols;
+         e += (int64_t)gridDim.x * blockDim.x) {
+        const int m = (int)(e / ncols), col = (int)(e % ncols);
+        const int t = col >> 7, r = col & 127, gl = r / (D + 1), q = r % (D + 1), i = t * n_i + gl;
+        double v = 0.0;
+        if (m < M && gl < n_i && i < D) v = (q < D) ? C[(int64_t)m * D + i] * (Xc[(int64_t)m * D + q] - s[q]) : C[(int64_t)m * D + i];
+        T[e] = v;
     }
 }
 
-template <int NT>
-static int launch_jacobian(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
-                           double* J, cudaStream_t st) {
-    using cfg = jac_cfg<NT>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        DVF_CUDA(cudaFuncSetAttribute(k_jacobian<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg::SMEM));
-        attr_set = true;
+__global__ void __launch_bounds__(JG_THREADS, 1)
+k_jacobian_gemm(const __grid_constant__ CUtensorMap mapT, const __grid_constant__ CUtensorMap mapK,
+                const double* __restrict__ x, const double* __restrict__ s, int64_t n_chunk, int64_t cell_base,
+                int64_t n_total, int D, int n_tiles, int k_stages, double scale, double* __restrict__ J) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned char* ring = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    double* vbuf = reinterpret_cast<double*>(ring + JG_STAGES * JG_STAGE_B);          // [JG_VROWS][128]
+    uint64_t* full = reinterpret_cast<uint64_t*>(vbuf + JG_VROWS * 128);
+    uint64_t* empty = full + JG_STAGES;
+    if (threadIdx.x == 0) {
+        for (int q = 0; q < JG_STAGES; ++q) { mbar_init(&full[q], 1); mbar_init(&empty[q], JG_CWARPS); }
+        mbar_fence_init();
     }
-    const unsigned grid = (unsigned)((n + cfg::CELLS - 1) / cfg::CELLS);
-    k_jacobian<NT><<<grid, JC_WARPS * 32, cfg::SMEM, st>>>(x, n, D, Xc, M, beta, C, J);
-    DVF_LAUNCH_CHECK();
-    return DVF_OK;
+    __syncthreads();
+
+    const int64_t n_cb = (n_chunk + 127) / 128, n_items = n_cb * n_tiles;
+    jg_ring rs{0, 0u};
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == JG_CWARPS) {
+        // ---------------- producer: one thread ----------------
+        if (lane != 0) return;
+        for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int t = (int)(item % n_tiles);
+            const int cb = (int)(item / n_tiles);
+            for (int ks = 0; ks < k_stages; ++ks) {
+                mbar_wait(&empty[rs.stage], rs.phase ^ 1u);
+                const unsigned sb = smem_u32(ring) + rs.stage * JG_STAGE_B, bar = smem_u32(&full[rs.stage]);
+                mbar_arrive_expect_tx(&full[rs.stage], JG_STAGE_B);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) tma_load_2d(sb + c * TMA_BOX_BYTES, &mapT, t * 128 + 16 * c, ks * JG_KC, bar);
+#pragma unroll
+                for (int c = 0; c < 8; ++c)   // box (mc, cg) = (c / 4, c % 4): 16 control points x 32 cells
+                    tma_load_2d(sb + (8 + c) * TMA_BOX_BYTES, &mapK, ks * JG_KC + 16 * (c >> 2), cb * 128 + 32 * (c & 3), bar);
+                jg_advance(rs);
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumers: warp (wi, wj) owns rows wi*32.., cells wj*32.. ----------------
+    const int g = lane >> 2, tq = lane & 3, wi = warp >> 2, wj = warp & 3;
+    // control point of k-step s, lane t:  m = 8 (s/2) + 2 (s&1) + (t&1) + 4 (t/2)
+    unsigned toffA[2][2], toffB[2][2];
+#pragma unroll
+    for (int sp = 0; sp < 2; ++sp) {
+        const int f = 2 * sp + (tq & 1) + 4 * (tq >> 1);      // (m & 7)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            // A box: row = control point, column = 8 h + g            (h = DMMA tile parity inside the 16-column box)
+            toffA[sp][h] = f * 128 + ((((h << 2) | (g >> 1)) ^ f) << 4) + (g & 1) * 8;
+            // B box: row = cell g (of an 8-cell tile), column = 8 h + 2 sp + (t&1) + 4 (t/2)   (h = (s/2) & 1)
+            toffB[sp][h] = g * 128 + (((4 * h + sp + 2 * (tq >> 1)) ^ g) << 4) + (tq & 1) * 8;
+        }
+    }
+    const unsigned wbaseA = (wi * 2) * TMA_BOX_BYTES;
+    const unsigned wbaseB = (8 + wj) * TMA_BOX_BYTES;
+    const int n_i = jg_ni(D);
+
+    for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int t = (int)(item % n_tiles);
+        const int64_t cb = item / n_tiles;
+        double acc[4][4][2];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[i][q][0] = acc[i][q][1] = 0.0;
+
+        for (int ks = 0; ks < k_stages; ++ks) {
+            mbar_wait(&full[rs.stage], rs.phase);
+            const unsigned char* sb = ring + rs.stage * JG_STAGE_B;
+#pragma unroll
+            for (int sk = 0; sk < 8; ++sk) {
+                const int sp = sk & 1;
+                double af[4], bf[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    af[i] = *reinterpret_cast<const double*>(sb + wbaseA + (i >> 1) * TMA_BOX_BYTES + (sk >> 1) * 1024 +
+                                                             toffA[sp][i & 1]);
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    bf[q] = *reinterpret_cast<const double*>(sb + wbaseB + (sk >> 2) * (4 * TMA_BOX_BYTES) + q * 1024 +
+                                                             toffB[sp][(sk >> 1) & 1]);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) dmma(acc[i][q][0], acc[i][q][1], af[i], bf[q]);
+            }
+            __syncwarp();
+            fence_proxy_async_smem();
+            if (lane == 0) mbar_arrive(&empty[rs.stage]);
+            jg_advance(rs);
+        }
+
+        // ---- epilogue: v rows -> shared, then J = scale * (v_i (x_j - s_j) - acc) ----
+        int rgl[4], re[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = wi * 32 + i * 8 + g;
+            rgl[i] = r / (D + 1);
+            re[i] = r % (D + 1);
+            if (rgl[i] >= n_i || t * n_i + rgl[i] >= D) rgl[i] = -1;     // padding row
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (rgl[i] >= 0 && re[i] == D) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    *reinterpret_cast<double2*>(vbuf + rgl[i] * 128 + wj * 32 + q * 8 + 2 * tq) =
+                        make_double2(acc[i][q][0], acc[i][q][1]);
+            }
+        named_barrier_sync(1, JG_CWARPS * 32);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int cl = wj * 32 + q * 8 + 2 * tq;
+            const int64_t c0 = cb * 128 + cl;                          // cell inside the chunk
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                if (rgl[i] < 0 || re[i] == D) continue;
+                const int gi = t * n_i + rgl[i], j = re[i];
+                const double2 v = *reinterpret_cast<const double2*>(vbuf + rgl[i] * 128 + cl);
+                const double sj = s[j];
+                double* out = J + ((int64_t)gi * D + j) * n_total + cell_base + c0;
+                if (c0 < n_chunk) out[0] = scale * (v.x * (x[(cell_base + c0) * D + j] - sj) - acc[i][q][0]);
+                if (c0 + 1 < n_chunk) out[1] = scale * (v.y * (x[(cell_base + c0 + 1) * D + j] - sj) - acc[i][q][1]);
+            }
+        }
+        named_barrier_sync(1, JG_CWARPS * 32);
+    }
 }
 
 }  // namespace dvf
@@ -160,15 +204,43 @@ extern "C" int dvf_jacobian(const double* x, int64_t n, int D, const double* Xc,
     DVF_ARG(D >= 1 && D <= kMaxD, "D=%d unsupported (1..%d)", D, kMaxD);
     DVF_ARG((x || n == 0) && Xc && C && (J || n == 0), "NULL pointer");
     if (n == 0) return DVF_OK;
+    static const bool direct = getenv("DVF_JAC_DIRECT") && atoi(getenv("DVF_JAC_DIRECT")) != 0;
+    if (direct) return dvf_jacobian_direct_impl(x, n, D, Xc, M, beta, C, J, stream);
+
     cudaStream_t st = (cudaStream_t)stream;
-    switch (pad8(D) / 8) {
-        case 1: return launch_jacobian<1>(x, n, D, Xc, M, beta, C, J, st);
-        case 2: return launch_jacobian<2>(x, n, D, Xc, M, beta, C, J, st);
-        case 3: return launch_jacobian<3>(x, n, D, Xc, M, beta, C, J, st);
-        case 4: return launch_jacobian<4>(x, n, D, Xc, M, beta, C, J, st);
-        case 5: return launch_jacobian<5>(x, n, D, Xc, M, beta, C, J, st);
-        case 6: return launch_jacobian<6>(x, n, D, Xc, M, beta, C, J, st);
-        case 7: return launch_jacobian<7>(x, n, D, Xc, M, beta, C, J, st);
-        default: return launch_jacobian<8>(x, n, D, Xc, M, beta, C, J, st);
+    static bool attr_set = false;
+    if (!attr_set) {
+        DVF_CUDA(cudaFuncSetAttribute(k_jacobian_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JG_SMEM));
+        attr_set = true;
     }
+    const int Mp = (M + JG_KC - 1) / JG_KC * JG_KC, n_i = jg_ni(D), n_tiles = (D + n_i - 1) / n_i, ncols = n_tiles * 128;
+    const int64_t chunk = n < JG_CHUNK ? n : JG_CHUNK;
+    // stream-ordered scratch: T_ext (Mp x ncols), centroid, K chunk (chunk x Mp)
+    const size_t t_bytes = ((size_t)Mp * ncols * 8 + 255) & ~(size_t)255, s_bytes = 1024;
+    char* scratch = nullptr;
+    DVF_CUDA(cudaMallocAsync(&scratch, t_bytes + s_bytes + (size_t)chunk * Mp * 8, st));
+    double* T = (double*)scratch;
+    double* sc = (double*)(scratch + t_bytes);
+    double* K = (double*)(scratch + t_bytes + s_bytes);
+    int rc = DVF_OK;
+    k_jg_centroid<<<(D + 63) / 64, 64, 0, st>>>(Xc, M, D, sc);
+    ++g_launch_count;
+    k_jg_build_t<<<num_sms() * 4, 256, 0, st>>>(Xc, C, sc, M, Mp, D, n_tiles, T);
+    ++g_launch_count;
+    CUtensorMap mapT, mapK;
+    rc = make_tmap_2d(&mapT, T, (uint64_t)ncols, (uint64_t)Mp, (uint64_t)ncols * 8);
+    for (int64_t c0 = 0; c0 < n && rc == DVF_OK; c0 += chunk) {
+        const int64_t nc = (n - c0 < chunk) ? (n - c0) : chunk;
+        rc = dvf_kernel_matrix_padded(x + c0 * D, nc, D, Xc, M, beta, K, Mp, stream);
+        if (rc) break;
+        rc = make_tmap_2d(&mapK, K, (uint64_t)Mp, (uint64_t)nc, (uint64_t)Mp * 8);
+        if (rc) break;
+        const int64_t n_items = (nc + 127) / 128 * n_tiles;
+        const int grid = (int)(n_items < num_sms() ? n_items : num_sms());
+        k_jacobian_gemm<<<grid, JG_THREADS, JG_SMEM, st>>>(mapT, mapK, x, sc, nc, c0, n, D, n_tiles, Mp / JG_KC, -2.0 * beta, J);
+        ++g_launch_count;
+        if (cudaGetLastError() != cudaSuccess) { rc = cuda_fail(cudaPeekAtLastError(), "k_jacobian_gemm", __LINE__); break; }
+    }
+    cudaFreeAsync(scratch, st);
+    return rc;
 }
