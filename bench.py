@@ -227,12 +227,20 @@ def run_ours(a):
 
     def step_e2e():
         """public numpy API: pinned host arrays in, numpy arrays out (single GPU path of the drop-in)"""
+        t = [time.perf_counter()]
         vfc = dvf.SvcVectorField(Xh, Vh, None, normalize=False, M=M, **em)
         vf = vfc.train()
+        t.append(time.perf_counter())
         J = dvf.Jacobian_rkhs_gaussian(Xh, vf)
+        t.append(time.perf_counter())
         div = vfc.compute_divergence()
+        t.append(time.perf_counter())
         acc, acc_mat = vfc.compute_acceleration()
+        t.append(time.perf_counter())
         curv, curv_mat = vfc.compute_curvature()
+        t.append(time.perf_counter())
+        state["e2e_stages_ms"] = {k: (t[i + 1] - t[i]) * 1e3 for i, k in enumerate(
+            ["train", "jacobian", "divergence", "acceleration", "curvature"])}
         h2d = 6 * Xh.nbytes                                 # X, V for the fit + X for each of the 4 evaluations
         d2h = (vf["V"].nbytes + vf["P"].nbytes + vf["C"].nbytes + J.nbytes + div.nbytes + acc.nbytes +
                acc_mat.nbytes + curv.nbytes + curv_mat.nbytes)
@@ -280,6 +288,7 @@ def run_ours(a):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e = {"value": world * N / float(t.item()), "unit": "cells/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": float(t.item()) * 1e3,
+               "stages_ms_last_step": state.get("e2e_stages_ms"),
                "note": "numpy API, pinned host inputs, numpy outputs incl. the %.1f GB Jacobian; N>1: one API job "
                        "per rank" % (J_buf.numel() * 8 / 1e9)}
 

@@ -42,6 +42,8 @@ SIGNATURES = {
     "dvf_kernel_matrix": (_i, [_p, _i64, _i, _p, _i, _d, _p, _i64, _p]),
     "dvf_eval": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
     "dvf_jacobian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
+    "dvf_jacobian_workspace_bytes": (_i, [_i64, _i, _i, C.POINTER(_sz)]),
+    "dvf_jacobian_ws": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p, _sz, _p]),
     "dvf_div_acc_curv": (_i, [_p, _i64, _i, _p, _i, _d, _p, _i, _p, _p, _p, _p, _p, _p, _p]),
     "dvf_gene_transform": (_i, [_p, _i64, _i, _p, _i, _p, _i, _i, _p, _i, _p, _p, _p]),
     "dvf_gene_transform_elem": (_i, [_p, _i64, _i, _p, _p, _p, _p]),
@@ -62,6 +64,7 @@ SIGNATURES = {
     "dvf_comm_destroy": (_i, [_p]),
     "dvf_comm_allreduce_sum": (_i, [_p, _p, _i64, _p]),
     "dvf_host_cdf": (_i, [_p, _i64, _p]),
+    "dvf_memcpy2d_async": (_i, [_p, _sz, _p, _sz, _sz, _sz, _i, _p]),
 }
 
 _lib = None

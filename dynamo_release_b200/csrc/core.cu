@@ -111,5 +111,14 @@ extern "C" int dvf_host_cdf(const double* p, int64_t n, double* cdf) {
     return DVF_OK;
 }
 
+extern "C" int dvf_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width_bytes,
+                                  size_t height, int to_host, void* stream) {
+    DVF_ARG(dst && src && dpitch >= width_bytes && spitch >= width_bytes, "bad argument");
+    if (width_bytes == 0 || height == 0) return DVF_OK;
+    DVF_CUDA(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width_bytes, height,
+                               to_host ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return DVF_OK;
+}
+
 extern "C" int dvf_abi_version(void) { return 1; }
 extern "C" const char* dvf_last_error(void) { return dvf::g_err; }

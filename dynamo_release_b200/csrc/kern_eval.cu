@@ -104,10 +104,15 @@ __global__ void __launch_bounds__(128) k_eval(const double* __restrict__ x, int6
         load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
         __syncthreads();
         for (int m = 0; m < mc; ++m) {
-            double d2 = 0.0;
+            // two interleaved partial sums: the FP64 pipe needs independent work behind every dependent DFMA
+            double d2a = 0.0, d2b = 0.0;
 #pragma unroll
-            for (int d = 0; d < DP; ++d) { double t = xr[d] - cs[m * DP + d]; d2 = fma(t, t, d2); }
-            const double k = exp(-beta * d2);
+            for (int d = 0; d < DP; d += 2) {
+                double ta = xr[d] - cs[m * DP + d], tb = xr[d + 1] - cs[m * DP + d + 1];
+                d2a = fma(ta, ta, d2a);
+                d2b = fma(tb, tb, d2b);
+            }
+            const double k = exp(-beta * (d2a + d2b));
 #pragma unroll
             for (int d = 0; d < DP; ++d) vr[d] = fma(k, Cs[m * DP + d], vr[d]);
         }
@@ -141,15 +146,17 @@ __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64
         load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
         __syncthreads();
         for (int m = 0; m < mc; ++m) {
-            double d2 = 0.0, t2 = 0.0;
+            double d2a = 0.0, d2b = 0.0, t2a = 0.0, t2b = 0.0;
 #pragma unroll
-            for (int d = 0; d < DP; ++d) {
-                double t = xr[d] - cs[m * DP + d];
-                d2 = fma(t, t, d2);
-                t2 = fma(t, Cs[m * DP + d], t2);
+            for (int d = 0; d < DP; d += 2) {
+                double ta = xr[d] - cs[m * DP + d], tb = xr[d + 1] - cs[m * DP + d + 1];
+                d2a = fma(ta, ta, d2a);
+                d2b = fma(tb, tb, d2b);
+                t2a = fma(ta, Cs[m * DP + d], t2a);
+                t2b = fma(tb, Cs[m * DP + d + 1], t2b);
             }
-            const double k = exp(-beta * d2);
-            div = fma(k, t2, div);
+            const double k = exp(-beta * (d2a + d2b));
+            div = fma(k, t2a + t2b, div);
 #pragma unroll
             for (int d = 0; d < DP; ++d) vr[d] = fma(k, Cs[m * DP + d], vr[d]);
         }
@@ -167,14 +174,16 @@ __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64
             load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
             __syncthreads();
             for (int m = 0; m < mc; ++m) {
-                double d2 = 0.0, s = 0.0;
+                double d2a = 0.0, d2b = 0.0, sa = 0.0, sb = 0.0;
 #pragma unroll
-                for (int d = 0; d < DP; ++d) {
-                    double t = xr[d] - cs[m * DP + d];
-                    d2 = fma(t, t, d2);
-                    s = fma(t, vr[d], s);
+                for (int d = 0; d < DP; d += 2) {
+                    double ta = xr[d] - cs[m * DP + d], tb = xr[d + 1] - cs[m * DP + d + 1];
+                    d2a = fma(ta, ta, d2a);
+                    d2b = fma(tb, tb, d2b);
+                    sa = fma(ta, vr[d], sa);
+                    sb = fma(tb, vr[d + 1], sb);
                 }
-                const double ks = exp(-beta * d2) * s;
+                const double ks = exp(-beta * (d2a + d2b)) * (sa + sb);
 #pragma unroll
                 for (int d = 0; d < DP; ++d) ar[d] = fma(ks, Cs[m * DP + d], ar[d]);
             }

@@ -198,49 +198,97 @@ k_jacobian_gemm(const __grid_constant__ CUtensorMap mapT, const __grid_constant_
 
 using namespace dvf;
 
-extern "C" int dvf_jacobian(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
-                            const double* C, double* J, void* stream) {
+static bool jacobian_uses_direct(int64_t n, int D, int M) {
+    // The GEMM form pays a K pre-pass and a 128-row tile granularity: it wins once the contraction is long and the
+    // tiles are full (measured on B200: 1M x 30, M=500: 39.9 vs 49.9 ms; 200k x 50, M=200: 11.6 vs 19.5 ms; but
+    // 100k x 30, M=100: 3.3 vs 1.7 ms).  DVF_JAC_DIRECT=1 / 0 forces one form (cross-checks, tools/jac_tune.py).
+    static const char* force = getenv("DVF_JAC_DIRECT");
+    return force ? atoi(force) != 0 : !(M >= 192 && D >= 12 && n >= 16384);
+}
+
+struct jg_layout { int Mp, n_tiles, ncols; int64_t chunk; size_t t_bytes, s_bytes, total; };
+static jg_layout jg_make_layout(int64_t n, int D, int M) {
+    jg_layout l;
+    l.Mp = (M + JG_KC - 1) / JG_KC * JG_KC;
+    const int n_i = jg_ni(D);
+    l.n_tiles = (D + n_i - 1) / n_i;
+    l.ncols = l.n_tiles * 128;
+    l.chunk = n < JG_CHUNK ? n : JG_CHUNK;
+    l.t_bytes = ((size_t)l.Mp * l.ncols * 8 + 255) & ~(size_t)255;
+    l.s_bytes = 1024;
+    l.total = l.t_bytes + l.s_bytes + (size_t)l.chunk * l.Mp * 8;
+    return l;
+}
+
+// scratch: T_ext (Mp x ncols) | centroid | K chunk (chunk x Mp)
+extern "C" int dvf_jacobian_workspace_bytes(int64_t n, int D, int M, size_t* out) {
+    DVF_ARG(out && n >= 0 && D >= 1 && D <= kMaxD && M >= 1, "bad argument");
+    *out = (n == 0 || jacobian_uses_direct(n, D, M)) ? 0 : jg_make_layout(n, D, M).total;
+    return DVF_OK;
+}
+
+extern "C" int dvf_jacobian_ws(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                               double* J, void* ws, size_t ws_bytes, void* stream) {
     DVF_ARG(n >= 0 && M >= 1, "n=%lld M=%d: need n >= 0, M >= 1", (long long)n, M);
     DVF_ARG(D >= 1 && D <= kMaxD, "D=%d unsupported (1..%d)", D, kMaxD);
     DVF_ARG((x || n == 0) && Xc && C && (J || n == 0), "NULL pointer");
     if (n == 0) return DVF_OK;
-    static const bool direct = getenv("DVF_JAC_DIRECT") && atoi(getenv("DVF_JAC_DIRECT")) != 0;
-    if (direct) return dvf_jacobian_direct_impl(x, n, D, Xc, M, beta, C, J, stream);
-
+    if (jacobian_uses_direct(n, D, M)) return dvf_jacobian_direct_impl(x, n, D, Xc, M, beta, C, J, stream);
+    const jg_layout l = jg_make_layout(n, D, M);
+    if (!ws || ws_bytes < l.total) {
+        set_error("jacobian workspace too small: %zu < %zu", ws_bytes, l.total);
+        return DVF_ERR_WORKSPACE;
+    }
+    DVF_ARG(((uintptr_t)ws & 255) == 0, "workspace must be 256-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
     static bool attr_set = false;
     if (!attr_set) {
         DVF_CUDA(cudaFuncSetAttribute(k_jacobian_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JG_SMEM));
         attr_set = true;
     }
-    const int Mp = (M + JG_KC - 1) / JG_KC * JG_KC, n_i = jg_ni(D), n_tiles = (D + n_i - 1) / n_i, ncols = n_tiles * 128;
-    const int64_t chunk = n < JG_CHUNK ? n : JG_CHUNK;
-    // stream-ordered scratch: T_ext (Mp x ncols), centroid, K chunk (chunk x Mp)
-    const size_t t_bytes = ((size_t)Mp * ncols * 8 + 255) & ~(size_t)255, s_bytes = 1024;
-    char* scratch = nullptr;
-    DVF_CUDA(cudaMallocAsync(&scratch, t_bytes + s_bytes + (size_t)chunk * Mp * 8, st));
+    char* scratch = (char*)ws;
     double* T = (double*)scratch;
-    double* sc = (double*)(scratch + t_bytes);
-    double* K = (double*)(scratch + t_bytes + s_bytes);
-    int rc = DVF_OK;
+    double* sc = (double*)(scratch + l.t_bytes);
+    double* K = (double*)(scratch + l.t_bytes + l.s_bytes);
     k_jg_centroid<<<(D + 63) / 64, 64, 0, st>>>(Xc, M, D, sc);
-    ++g_launch_count;
-    k_jg_build_t<<<num_sms() * 4, 256, 0, st>>>(Xc, C, sc, M, Mp, D, n_tiles, T);
-    ++g_launch_count;
+    DVF_LAUNCH_CHECK();
+    k_jg_build_t<<<num_sms() * 4, 256, 0, st>>>(Xc, C, sc, M, l.Mp, D, l.n_tiles, T);
+    DVF_LAUNCH_CHECK();
     CUtensorMap mapT, mapK;
-    rc = make_tmap_2d(&mapT, T, (uint64_t)ncols, (uint64_t)Mp, (uint64_t)ncols * 8);
-    for (int64_t c0 = 0; c0 < n && rc == DVF_OK; c0 += chunk) {
-        const int64_t nc = (n - c0 < chunk) ? (n - c0) : chunk;
-        rc = dvf_kernel_matrix_padded(x + c0 * D, nc, D, Xc, M, beta, K, Mp, stream);
-        if (rc) break;
-        rc = make_tmap_2d(&mapK, K, (uint64_t)Mp, (uint64_t)nc, (uint64_t)Mp * 8);
-        if (rc) break;
-        const int64_t n_items = (nc + 127) / 128 * n_tiles;
+    if (int rc = make_tmap_2d(&mapT, T, (uint64_t)l.ncols, (uint64_t)l.Mp, (uint64_t)l.ncols * 8)) return rc;
+    for (int64_t c0 = 0; c0 < n; c0 += l.chunk) {
+        const int64_t nc = (n - c0 < l.chunk) ? (n - c0) : l.chunk;
+        if (int rc = dvf_kernel_matrix_padded(x + c0 * D, nc, D, Xc, M, beta, K, l.Mp, stream)) return rc;
+        if (int rc = make_tmap_2d(&mapK, K, (uint64_t)l.Mp, (uint64_t)nc, (uint64_t)l.Mp * 8)) return rc;
+        const int64_t n_items = (nc + 127) / 128 * l.n_tiles;
         const int grid = (int)(n_items < num_sms() ? n_items : num_sms());
-        k_jacobian_gemm<<<grid, JG_THREADS, JG_SMEM, st>>>(mapT, mapK, x, sc, nc, c0, n, D, n_tiles, Mp / JG_KC, -2.0 * beta, J);
-        ++g_launch_count;
-        if (cudaGetLastError() != cudaSuccess) { rc = cuda_fail(cudaPeekAtLastError(), "k_jacobian_gemm", __LINE__); break; }
+        k_jacobian_gemm<<<grid, JG_THREADS, JG_SMEM, st>>>(mapT, mapK, x, sc, nc, c0, n, D, l.n_tiles, l.Mp / JG_KC,
+                                                           -2.0 * beta, J);
+        DVF_LAUNCH_CHECK();
     }
-    cudaFreeAsync(scratch, st);
+    return DVF_OK;
+}
+
+// convenience form without a caller workspace: scratch comes from the device's stream-ordered pool, whose release
+// threshold is raised once so that the 0.5 GB chunk buffer is not returned to the driver at every synchronisation
+extern "C" int dvf_jacobian(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
+                            const double* C, double* J, void* stream) {
+    size_t bytes = 0;
+    if (int rc = dvf_jacobian_workspace_bytes(n, D, M, &bytes)) return rc;
+    if (bytes == 0) return dvf_jacobian_ws(x, n, D, Xc, M, beta, C, J, nullptr, 0, stream);
+    static bool pool_set = false;
+    if (!pool_set) {
+        int dev = 0;
+        cudaMemPool_t pool;
+        DVF_CUDA(cudaGetDevice(&dev));
+        DVF_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+        uint64_t thr = ~0ull;
+        DVF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+        pool_set = true;
+    }
+    void* ws = nullptr;
+    DVF_CUDA(cudaMallocAsync(&ws, bytes, (cudaStream_t)stream));
+    const int rc = dvf_jacobian_ws(x, n, D, Xc, M, beta, C, J, ws, bytes, stream);
+    cudaFreeAsync(ws, (cudaStream_t)stream);
     return rc;
 }

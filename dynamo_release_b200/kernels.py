@@ -46,8 +46,59 @@ def jacobian(x, Xc, beta, Cm, out=None):
     x, Xc, Cm = _field(x, Xc, Cm)
     n, D = x.shape
     J = empty((D, D, n)) if out is None else out
-    _lib.check(lib().dvf_jacobian(ptr(x), n, D, ptr(Xc), Xc.shape[0], float(beta), ptr(Cm), ptr(J), stream_ptr()))
+    M = Xc.shape[0]
+    nbytes = C.c_size_t(0)
+    _lib.check(lib().dvf_jacobian_workspace_bytes(n, D, M, C.byref(nbytes)))
+    # workspace from torch's caching allocator (stream-ordered reuse, no driver allocation in the steady state)
+    ws = torch.empty((nbytes.value + 7) // 8, dtype=torch.float64, device="cuda") if nbytes.value else None
+    _lib.check(lib().dvf_jacobian_ws(ptr(x), n, D, ptr(Xc), M, float(beta), ptr(Cm), ptr(J), ptr(ws), nbytes.value,
+                                     stream_ptr()))
     return J
+
+
+JAC_STREAM_CHUNK = 131072     # cells per streamed slab (the GEMM kernel's own K chunk)
+
+
+def jacobian_to_host(x, Xc, beta, Cm):
+    """K6 with the result delivered as a NumPy array (D, D, n): cell slabs are computed into two device buffers in
+    turn and copied to pinned host memory on a second stream while the next slab is computed, so the PCIe transfer
+    of the 8 D^2 n bytes overlaps the GEMM and the full Jacobian never has to exist in HBM."""
+    x, Xc, Cm = _field(x, Xc, Cm)
+    n, D = x.shape
+    Jh = torch.empty((D, D, n), dtype=torch.float64, pin_memory=True)
+    if n == 0:
+        return Jh.numpy()
+    ch = min(JAC_STREAM_CHUNK, n)
+    bufs = [torch.empty((D * D * ch,), dtype=torch.float64, device="cuda") for _ in range(2 if n > ch else 1)]
+    main, side = torch.cuda.current_stream(), _side_stream()
+    copied = [None, None]
+    L = lib()
+    for k, c0 in enumerate(range(0, n, ch)):
+        nc = min(ch, n - c0)
+        b = k % len(bufs)
+        if copied[b] is not None:
+            main.wait_event(copied[b])           # the slab buffer is free again
+        slab = bufs[b][:D * D * nc].view(D, D, nc)
+        jacobian(x[c0:c0 + nc], Xc, beta, Cm, out=slab)
+        done = torch.cuda.Event()
+        done.record(main)
+        side.wait_event(done)
+        _lib.check(L.dvf_memcpy2d_async(Jh.data_ptr() + c0 * 8, n * 8, slab.data_ptr(), nc * 8, nc * 8, D * D, 1,
+                                        side.cuda_stream))
+        copied[b] = torch.cuda.Event()
+        copied[b].record(side)
+    side.synchronize()
+    return Jh.numpy()
+
+
+_SIDE = {}
+
+
+def _side_stream():
+    d = torch.cuda.current_device()
+    if d not in _SIDE:
+        _SIDE[d] = torch.cuda.Stream(device=d)
+    return _SIDE[d]
 
 
 def div_acc_curv(x, Xc, beta, Cm, formula=2, want=("v", "div", "acc", "acc_norm", "curv", "curv_norm")):

@@ -14,6 +14,17 @@ from . import _lib, kernels, prelude
 from .device import dev, empty, host, lib, ptr, stream_ptr
 
 
+_POOL = None
+
+
+def _copy_pool():
+    global _POOL
+    if _POOL is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _POOL = ThreadPoolExecutor(max_workers=2, thread_name_prefix="dvf-host-copy")
+    return _POOL
+
+
 class FitState:
     """Device-resident result of a fit (benchmark mode: nothing is copied back unless asked)."""
 
@@ -66,7 +77,9 @@ def SparseVFC(X, Y, Grid, M=100, a=5, beta=None, ecr=1e-5, gamma=0.9, lambda_=3,
     on the device in every case)."""
     if div_cur_free_kernels:
         raise NotImplementedError("div_cur_free_kernels=True is outside the B200 hot path (Gaussian kernel only)")
-    X_ori, Y_ori = np.array(X, copy=True), np.array(Y, copy=True)  # reference copies its inputs (:396)
+    # the reference copies its inputs (:396); the two host copies run on helper threads (NumPy releases the GIL)
+    # while this thread uploads the data and drives the GPU
+    copies = _copy_pool().map(lambda a: np.array(a, copy=True), (X, Y))
     Xd, Yd = dev(X), dev(Y)
     valid, Xv, Yv, ctrl, idx, beta = prelude.run(Xd, Yd, M, seed=seed, beta=beta,
                                                  velocity_based_sampling=velocity_based_sampling)
@@ -83,6 +96,7 @@ def SparseVFC(X, Y, Grid, M=100, a=5, beta=None, ecr=1e-5, gamma=0.9, lambda_=3,
             f"tecr must larger than ecr and sigma2 must larger than 1e-8"
         )
     i = st.n_iter
+    X_ori, Y_ori = list(copies)
     Cm = host(st.C)
     P = host(st.P).reshape(-1, 1)
     grid_V = None

@@ -87,6 +87,8 @@ def Jacobian_rkhs_gaussian(x, vf_dict, vectorize=False, device_out=False):
     """reference vectorfield/utils.py:351-379.  (D, D, n) for 2-d x, (D, D) for 1-d x."""
     Xc, beta, C = _vf_parts(vf_dict)
     x2, single = _as2d(x)
+    if not device_out and not single:
+        return kernels.jacobian_to_host(x2, Xc, beta, C)   # slabs stream to pinned host memory behind the GEMM
     J = kernels.jacobian(x2, Xc, beta, C)
     if single:
         J = J[:, :, 0]

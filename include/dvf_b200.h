@@ -51,6 +51,11 @@ int dvf_eval(const double* x, int64_t n, int D, const double* Xc, int M, double 
  * fastest.  replaces vectorfield/utils.py:351-379 (Jacobian_rkhs_gaussian). */
 int dvf_jacobian(const double* x, int64_t n, int D, const double* Xc, int M, double beta,
                  const double* C, double* J, void* stream);
+/* The same with a caller-owned workspace (query, then pass; 256-byte aligned; 0 bytes when the direct per-cell
+ * kernel is used).  dvf_jacobian() takes its scratch from the device's stream-ordered memory pool instead. */
+int dvf_jacobian_workspace_bytes(int64_t n, int D, int M, size_t* out);
+int dvf_jacobian_ws(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                    double* J, void* ws, size_t ws_bytes, void* stream);
 
 /* K7: fused divergence / acceleration / curvature without materialising J.  Any output may be NULL.
  *   v (n x D) = f(x);  div (n) = tr J;  acc (n x D) = J v;  acc_norm (n) = |acc|;
@@ -148,6 +153,12 @@ int dvf_comm_unique_id(void* out128);                          /* rank 0: 128-by
 int dvf_comm_init(const void* id128, int rank, int world, void** comm);
 int dvf_comm_destroy(void* comm);
 int dvf_comm_allreduce_sum(void* comm, double* buf, int64_t count, void* stream);
+
+/* Strided (pitched) asynchronous copy between device and pinned host memory: `height` rows of `width_bytes`.
+ * Used to stream the (D, D, n) Jacobian to the host in cell chunks while the next chunk is computed.
+ * to_host != 0: device -> host, else host -> device. */
+int dvf_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width_bytes, size_t height,
+                       int to_host, void* stream);
 
 /* ---- host helper of the prelude -------------------------------------------------------------------------
  * Control-point sampling (reference tools/sampling.py:242-245 -> numpy Generator.choice(p=..., replace=False)):

@@ -195,6 +195,28 @@ def test_large_properties_linearity_and_consistency(pkg):
     assert rel(_np(J[:, :, sl]), o.jacobian(x[sl], vf)) < 1e-11
 
 
+def test_jacobian_gemm_form_chunks_and_pool_entry(pkg):
+    """GEMM-form Jacobian across a K-chunk boundary (131072 cells), ragged last tile, data far from the origin
+    (the shift s is the control-point centroid), D = 50; the workspace entry point and the pool entry point agree
+    bit for bit and match the oracle's direct formula."""
+    from dynamo_release_b200 import kernels
+    from dynamo_release_b200.device import dev, empty, lib, ptr, stream_ptr
+    from dynamo_release_b200 import _lib
+
+    rng = np.random.default_rng(11)
+    n, D, M = 131072 + 1077, 50, 200
+    x = rng.normal(size=(n, D)) * 1.5 + 40.0
+    vf = {"X_ctrl": x[rng.choice(n, M, replace=False)] + 0.01, "beta": 0.004, "C": rng.normal(size=(M, D))}
+    xd, Xc, Cm = dev(x), dev(vf["X_ctrl"]), dev(vf["C"])
+    J = kernels.jacobian(xd, Xc, vf["beta"], Cm)
+    J2 = empty((D, D, n))
+    _lib.check(lib().dvf_jacobian(ptr(xd), n, D, ptr(Xc), M, float(vf["beta"]), ptr(Cm), ptr(J2), stream_ptr()))
+    assert torch.equal(J, J2)
+    for sl in (slice(0, 24), slice(131072 - 12, 131072 + 12), slice(n - 24, n)):
+        assert rel(_np(J[:, :, sl]), o.jacobian(x[sl], vf)) < 1e-11
+    assert bool(torch.isfinite(J).all())
+
+
 def test_edge_cases(pkg):
     rng = np.random.default_rng(1)
     vf = {"X_ctrl": rng.normal(size=(7, 3)), "beta": 0.3, "C": rng.normal(size=(7, 3))}
