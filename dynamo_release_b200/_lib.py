@@ -46,6 +46,8 @@ SIGNATURES = {
     "dvf_jacobian_ws": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p, _sz, _p]),
     "dvf_div_acc_curv": (_i, [_p, _i64, _i, _p, _i, _d, _p, _i, _p, _p, _p, _p, _p, _p, _p]),
     "dvf_gene_transform": (_i, [_p, _i64, _i, _p, _i, _p, _i, _i, _p, _i, _p, _p, _p]),
+    "dvf_gene_gemm_workspace_bytes": (_i, [_i64, _i, _i, _i, _i, _i, C.POINTER(_sz)]),
+    "dvf_gene_transform_gemm": (_i, [_p, _i64, _i, _p, _i, _p, _i, _i, _p, _i, _p, _p, _p, _sz, _p]),
     "dvf_gene_transform_elem": (_i, [_p, _i64, _i, _p, _p, _p, _p]),
     "dvf_vector_transform": (_i, [_p, _i64, _i, _p, _i, _p, _p]),
     "dvf_fit_row_width": (_i64, [_i, _i]),

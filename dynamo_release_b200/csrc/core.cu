@@ -51,6 +51,36 @@ int make_tmap_2d(CUtensorMap* map, const void* base, uint64_t cols, uint64_t row
     return encode_2d(map, base, cols, rows, pitch_bytes, TMA_BOX_COLS, TMA_BOX_ROWS, CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
 }
+int make_tmap_3d(CUtensorMap* map, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1_bytes,
+                 uint64_t stride2_bytes) {
+    encode_tiled_fn enc = get_encode_tiled();
+    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return DVF_ERR_CUDA; }
+    if (((uintptr_t)base & 15) != 0 || (stride1_bytes & 15) != 0 || (stride2_bytes & 15) != 0) {
+        set_error("TMA source needs a 16-byte aligned base and strides");
+        return DVF_ERR_ARG;
+    }
+    const cuuint64_t dims[3] = {d0, d1, d2}, strides[2] = {stride1_bytes, stride2_bytes};
+    const cuuint32_t box[3] = {TMA_BOX_COLS, 1, TMA_BOX_ROWS}, estr[3] = {1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (rank 3) failed: %d", (int)r); return DVF_ERR_CUDA; }
+    return DVF_OK;
+}
+int pool_alloc(void** p, size_t bytes, cudaStream_t st) {
+    static bool pool_set = false;
+    if (!pool_set) {
+        int dev = 0;
+        cudaMemPool_t pool;
+        DVF_CUDA(cudaGetDevice(&dev));
+        DVF_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+        uint64_t thr = ~0ull;
+        DVF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+        pool_set = true;
+    }
+    DVF_CUDA(cudaMallocAsync(p, bytes, st));
+    return DVF_OK;
+}
 int make_tmap_vec(CUtensorMap* map, const void* base, uint64_t n) {
     // rank 2 with a single row (a rank-1 map is rejected without a stride array)
     return encode_2d(map, base, n, 1, (n * 8 + 15) & ~(uint64_t)15, 32, 1, CU_TENSOR_MAP_SWIZZLE_NONE,

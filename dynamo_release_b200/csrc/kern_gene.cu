@@ -3,7 +3,9 @@
 // Factored as T_e[j][c] = sum_i Qe[e][i] J[i][j][c]  (D^2 flops per (e, c)), then
 // out[e][r][c] = sum_j Qr[r][j] T_e[j][c]; one CTA = one effector x 32 cells, T_e lives in shared memory,
 // every global access is a 32-cell (256 B / 128 B) run along the cell-fastest layouts of J and out.
+#include <cstdlib>
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace dvf {
 
@@ -134,6 +136,23 @@ extern "C" int dvf_gene_transform(const double* J, int64_t n, int D, const doubl
     DVF_ARG(!out_group_sum || (group && n_groups >= 1), "group labels missing");
     DVF_ARG(Ge <= 65535, "Ge > 65535: split the effector set");
     if (n == 0) return DVF_OK;
+    // large gene sets: two batched DGEMMs on the FP64 tensor cores (kern_gene_gemm.cu); its 128-row tiles would be
+    // mostly empty for short gene lists, which stay on the per-effector kernel below.  DVF_GENE_GEMM=0/1 forces a path.
+    {
+        static const char* force = getenv("DVF_GENE_GEMM");
+        const bool ok = (n % 2) == 0 && ((uintptr_t)J & 15) == 0 && D <= kMaxD;
+        const bool want = force ? atoi(force) != 0 : (Ge >= 96 && Gr >= 96 && n >= 128);
+        if (ok && want) {
+            size_t bytes = 0;
+            if (int rc = dvf_gene_gemm_workspace_bytes(n, D, Ge, Gr, out_full != nullptr, out_group_sum != nullptr, &bytes)) return rc;
+            void* ws = nullptr;
+            if (int rc = pool_alloc(&ws, bytes, (cudaStream_t)stream)) return rc;
+            const int rc = dvf_gene_transform_gemm(J, n, D, Qe, Ge, Qr, Gr, take_abs, group, n_groups, out_full, out_group_sum,
+                                                   ws, bytes, stream);
+            cudaFreeAsync(ws, (cudaStream_t)stream);
+            return rc;
+        }
+    }
     const size_t smem = sizeof(double) * ((size_t)D * GT_CELLS + D);
     DVF_ARG(smem <= 200 * 1024, "D too large for the gene transform");
     if (smem > 48 * 1024)

@@ -276,18 +276,8 @@ extern "C" int dvf_jacobian(const double* x, int64_t n, int D, const double* Xc,
     size_t bytes = 0;
     if (int rc = dvf_jacobian_workspace_bytes(n, D, M, &bytes)) return rc;
     if (bytes == 0) return dvf_jacobian_ws(x, n, D, Xc, M, beta, C, J, nullptr, 0, stream);
-    static bool pool_set = false;
-    if (!pool_set) {
-        int dev = 0;
-        cudaMemPool_t pool;
-        DVF_CUDA(cudaGetDevice(&dev));
-        DVF_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
-        uint64_t thr = ~0ull;
-        DVF_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
-        pool_set = true;
-    }
     void* ws = nullptr;
-    DVF_CUDA(cudaMallocAsync(&ws, bytes, (cudaStream_t)stream));
+    if (int rc = pool_alloc(&ws, bytes, (cudaStream_t)stream)) return rc;
     const int rc = dvf_jacobian_ws(x, n, D, Xc, M, beta, C, J, ws, bytes, stream);
     cudaFreeAsync(ws, (cudaStream_t)stream);
     return rc;

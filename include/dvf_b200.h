@@ -75,6 +75,12 @@ int dvf_div_acc_curv(const double* x, int64_t n, int D, const double* Xc, int M,
 int dvf_gene_transform(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr,
                        int Gr, int take_abs, const int32_t* group, int n_groups, float* out_full,
                        double* out_group_sum, void* stream);
+/* Tensor-core path of K8 with a caller-owned workspace (1024-byte aligned); dvf_gene_transform() selects it for
+ * large gene sets (Ge, Gr >= 96) and takes the workspace from the stream-ordered pool.  Needs an even n. */
+int dvf_gene_gemm_workspace_bytes(int64_t n, int D, int Ge, int Gr, int full, int grouped, size_t* out);
+int dvf_gene_transform_gemm(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr, int Gr,
+                            int take_abs, const int32_t* group, int n_groups, float* out_full,
+                            double* out_group_sum, void* ws, size_t ws_bytes, void* stream);
 int dvf_gene_transform_elem(const double* J, int64_t n, int D, const double* qe, const double* qr,
                             double* out_elem, void* stream);
 

@@ -70,6 +70,14 @@ def test_gene_space_transforms(pkg, name):
     assert out.dtype == np.float32 and out.shape == ref.shape
     ulp = np.abs(out.astype(np.float64) - ref.astype(np.float64)) / np.maximum(np.spacing(np.abs(ref)), 1e-45)
     assert ulp.max() <= 1.0, "float32 result differs by more than 1 ulp"
+    # top-k regulator ranking per effector (what rank_jacobian_genes 'full reg' sorts: mean over cells, rank_vf.py:497)
+    # from our float32 array equals the ranking from the reference's array
+    k = min(5, ref.shape[1])
+    for take_abs in (False, True):
+        a, b = (np.abs(out), np.abs(ref)) if take_abs else (out, ref)
+        ra = np.argsort(-np.mean(a, axis=2), axis=1, kind="stable")[:, :k]
+        rb = np.argsort(-np.mean(b, axis=2), axis=1, kind="stable")[:, :k]
+        assert np.array_equal(ra, rb)
     assert rel(pkg.elementwise_jacobian_transformation(Jg, Q[1], Q[5]), g["gene_elem"]) < 1e-12
     assert rel(pkg.vector_transformation(g["calc_acc_mat"], Q), g["gene_vec"]) < 1e-13
     # fused |.| group mean == mean of the materialised array
@@ -77,6 +85,30 @@ def test_gene_space_transforms(pkg, name):
     gm = pkg.average_jacobian_by_group(Jg, Q[: ng // 2], Q[ng // 3:], lab, 3, take_abs=True)
     want = np.stack([np.abs(ref[:, :, lab == k]).astype(np.float64).mean(2) for k in range(3)])
     assert rel(gm, want) < 1e-12
+
+
+def test_gene_transform_tensor_core_path(pkg):
+    """Large gene sets take the two-stage DGEMM path (Ge, Gr >= 96): float32 result within 1 ulp of the float64
+    einsum, group sums equal to sums of the materialised float32 array, ragged tiles in every dimension."""
+    from dynamo_release_b200 import kernels
+    rng = np.random.default_rng(21)
+    D, n, Ge, Gr = 50, 2 * 173, 200, 131
+    J = rng.normal(size=(D, D, n))
+    Qe, Qr = rng.normal(size=(Ge, D)) / 7, rng.normal(size=(Gr, D)) / 7
+    ref64 = np.einsum("ei,ijc,rj->erc", Qe, J, Qr, optimize=True)
+    ref = ref64.astype(np.float32)
+    out, _ = kernels.gene_transform(J, Qe, Qr)
+    out = _np(out)
+    assert out.dtype == np.float32 and out.shape == ref.shape
+    ulp = np.abs(out.astype(np.float64) - ref64) / np.maximum(np.spacing(np.abs(ref)).astype(np.float64), 1e-45)
+    assert ulp.max() <= 1.0 + 1e-6, "float32 result differs by more than 1 ulp from the float64 value"
+    lab = (np.arange(n) * 7) % 5
+    full, gs = kernels.gene_transform(J, Qe, Qr, take_abs=True, group=lab, n_groups=5, full=True)
+    _, gs_only = kernels.gene_transform(J, Qe, Qr, take_abs=True, group=lab, n_groups=5, full=False)
+    full = _np(full)
+    assert np.array_equal(full, np.abs(out))
+    want = np.stack([full[:, :, lab == k].astype(np.float64).sum(2) for k in range(5)])
+    assert rel(_np(gs), want) < 1e-13 and rel(_np(gs_only), want) < 1e-13
 
 
 def _exact_solve(A, B):
