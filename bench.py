@@ -28,6 +28,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+GRAM_DRAM_BYTES_NCU = 12.95e9   # 11.52 GB read + 1.43 GB written (partial tiles), ncu, round 1
 FP64_PEAK_TFLOPS = 37.1   # DMMA m8n8k4 chain measured on this pool's B200 (tools/fp64_peak.cu, profiles/fp64_peak_r01.json)
 
 
@@ -314,9 +315,13 @@ def run_ours(a):
                           for i, k in enumerate(["prelude", "fit", "jacobian", "div_acc_curv"])},
             "e2e": e2e,
             "gpu_launches": int(launches.value),
-            "roofline": {"bound": "tensor", "kernel": "k_gram (weighted Gram + RHS, FP64 DMMA m8n8k4) + k_gram_reduce",
+            "roofline": {"bound": "tensor", "kernel": "k_gram (weighted Gram + RHS, FP64 DMMA m8n8k4 fed by TMA) + k_gram_reduce",
                          "achieved": achieved, "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s",
-                         "frac": achieved / FP64_PEAK_TFLOPS, "traffic": None,
+                         "frac": achieved / FP64_PEAK_TFLOPS,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one k_gram launch at the default workload from
+                         # the committed ncu --set full capture (profiles/ncu_k_gram_r01_details.txt); null elsewhere
+                         "traffic": GRAM_DRAM_BYTES_NCU if (N, D, M) == (1_000_000, 30, 500) else None,
+                         "traffic_unit": "bytes per launch (compulsory: %d)" % (N * kernels.row_width(M, D) * 8),
                          "ms_per_launch": per_launch_ms, "launches_timed": a.steps * n_iter,
                          "share_of_step": gram_ms.value / a.steps / ms,
                          "peak_source": "FP64 DMMA peak measured on this pool (tools/fp64_peak.cu: 37.1 TFLOP/s; "

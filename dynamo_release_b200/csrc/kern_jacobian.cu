@@ -11,8 +11,9 @@
 //   pre-pass : K = exp(-beta |x - c|^2) for a chunk of cells (k_kernel_matrix, direct distance form like cdist)
 //   GEMM     : persistent CTAs, 16 consumer warps (32 x 32 block each, 128 rows x 128 cells per item) + 1 TMA producer
 //              thread, 3-stage ring of 32 control points, 128-byte swizzled boxes; the k-step -> control-point mapping
-//              m(s, t) = 8 (s/2) + 2 (s&1) + (t&1) + 4 (t/2) makes both the A loads (control point = box row) and the
-//              B loads (control point = box column) bank-conflict free.
+//              m(s, t) = 8 (s/2) + 2 (s&1) + (t&1) + 4 (t/2) together with the in-tile row permutation (g0, g2, g1)
+//              makes both the A loads (control point = box row) and the B loads (control point = box column)
+//              bank-conflict free (ncu: 4 -> 2 shared wavefronts per LDS.64).
 // The direct per-cell form (kern_jacobian_direct.cu) is kept for cross-checks: DVF_JAC_DIRECT=1.
 #include <cstdlib>
 #include "common.cuh"
@@ -106,16 +107,20 @@ k_jacobian_gemm(const __grid_constant__ CUtensorMap mapT, const __grid_constant_
     // ---------------- consumers: warp (wi, wj) owns rows wi*32.., cells wj*32.. ----------------
     const int g = lane >> 2, tq = lane & 3, wi = warp >> 2, wj = warp & 3;
     // control point of k-step s, lane t:  m = 8 (s/2) + 2 (s&1) + (t&1) + 4 (t/2)
+    // DMMA row/column g of a tile is row / cell pg = (g0, g2, g1) of the 8-row group (bits 1 and 2 swapped): with the
+    // 128-byte swizzle this puts the 16 lanes of each half-warp on 16 distinct 8-byte bank pairs for A and for B
+    const int pg = (g & 1) | (((g >> 1) & 1) << 2) | ((g >> 2) << 1);
+    const int pc = 4 * (tq & 1) + 2 * (tq >> 1);             // cells pc, pc + 1 of a tile are this lane's accumulators
     unsigned toffA[2][2], toffB[2][2];
 #pragma unroll
     for (int sp = 0; sp < 2; ++sp) {
         const int f = 2 * sp + (tq & 1) + 4 * (tq >> 1);      // (m & 7)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            // A box: row = control point, column = 8 h + g            (h = DMMA tile parity inside the 16-column box)
-            toffA[sp][h] = f * 128 + ((((h << 2) | (g >> 1)) ^ f) << 4) + (g & 1) * 8;
-            // B box: row = cell g (of an 8-cell tile), column = 8 h + 2 sp + (t&1) + 4 (t/2)   (h = (s/2) & 1)
-            toffB[sp][h] = g * 128 + (((4 * h + sp + 2 * (tq >> 1)) ^ g) << 4) + (tq & 1) * 8;
+            // A box: row = control point, column = 8 h + pg           (h = DMMA tile parity inside the 16-column box)
+            toffA[sp][h] = f * 128 + ((((h << 2) | (pg >> 1)) ^ f) << 4) + (pg & 1) * 8;
+            // B box: row = cell pg (of an 8-cell tile), column = 8 h + 2 sp + (t&1) + 4 (t/2)   (h = (s/2) & 1)
+            toffB[sp][h] = pg * 128 + (((4 * h + sp + 2 * (tq >> 1)) ^ pg) << 4) + (tq & 1) * 8;
         }
     }
     const unsigned wbaseA = (wi * 2) * TMA_BOX_BYTES;
@@ -161,7 +166,7 @@ k_jacobian_gemm(const __grid_constant__ CUtensorMap mapT, const __grid_constant_
         int rgl[4], re[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const int r = wi * 32 + i * 8 + g;
+            const int r = wi * 32 + i * 8 + pg;
             rgl[i] = r / (D + 1);
             re[i] = r % (D + 1);
             if (rgl[i] >= n_i || t * n_i + rgl[i] >= D) rgl[i] = -1;     // padding row
@@ -171,13 +176,13 @@ k_jacobian_gemm(const __grid_constant__ CUtensorMap mapT, const __grid_constant_
             if (rgl[i] >= 0 && re[i] == D) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
-                    *reinterpret_cast<double2*>(vbuf + rgl[i] * 128 + wj * 32 + q * 8 + 2 * tq) =
+                    *reinterpret_cast<double2*>(vbuf + rgl[i] * 128 + wj * 32 + q * 8 + pc) =
                         make_double2(acc[i][q][0], acc[i][q][1]);
             }
         named_barrier_sync(1, JG_CWARPS * 32);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const int cl = wj * 32 + q * 8 + 2 * tq;
+            const int cl = wj * 32 + q * 8 + pc;
             const int64_t c0 = cb * 128 + cl;                          // cell inside the chunk
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
