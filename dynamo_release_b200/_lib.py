@@ -66,6 +66,7 @@ SIGNATURES = {
     "dvf_comm_destroy": (_i, [_p]),
     "dvf_comm_allreduce_sum": (_i, [_p, _p, _i64, _p]),
     "dvf_host_cdf": (_i, [_p, _i64, _p]),
+    "dvf_host_scale": (_i, [_p, _i64, C.c_double, _p]),
     "dvf_memcpy2d_async": (_i, [_p, _sz, _p, _sz, _sz, _sz, _i, _p]),
 }
 

@@ -1,6 +1,9 @@
 // Error plumbing and ABI version of libdvf_b200.
 #include "common.cuh"
 #include "tma.cuh"
+#include <algorithm>
+#include <thread>
+#include <vector>
 
 namespace dvf {
 static thread_local char g_err[512] = "";
@@ -131,13 +134,36 @@ extern "C" int dvf_profile_get(double* gram_ms, int* gram_launches, long long* k
     return DVF_OK;
 }
 
-// numpy.cumsum(p) followed by cdf /= cdf[-1] (Generator.choice, replace=False): one sequential pass + one SIMD pass
+// element-wise host passes of the sampling helper, split over a few threads once they are long enough to matter
+// (8M cells on rank 0 of an 8-GPU job); every element is computed exactly as the scalar loop would
+template <typename F>
+static void host_parallel_for(int64_t n, F body) {
+    const int64_t grain = 1 << 19;
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<int64_t>(std::min<int64_t>(hw ? hw : 1, 8), (n + grain - 1) / grain);
+    if (nt <= 1) { body((int64_t)0, n); return; }
+    std::vector<std::thread> th;
+    const int64_t per = (n + nt - 1) / nt;
+    for (int t = 1; t < nt; ++t) th.emplace_back([=] { body(std::min(n, t * per), std::min(n, (t + 1) * per)); });
+    body((int64_t)0, std::min(n, per));
+    for (auto& x : th) x.join();
+}
+
+// p = v / total (tools/sampling.py:244)
+extern "C" int dvf_host_scale(const double* v, int64_t n, double total, double* p) {
+    DVF_ARG(v && p && n >= 0, "bad argument");
+    host_parallel_for(n, [=](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) p[i] = v[i] / total; });
+    return DVF_OK;
+}
+
+// numpy.cumsum(p) followed by cdf /= cdf[-1] (Generator.choice, replace=False): one strictly sequential pass (the
+// rounding of every partial sum matters to searchsorted) + one element-wise pass
 extern "C" int dvf_host_cdf(const double* p, int64_t n, double* cdf) {
     DVF_ARG(p && cdf && n >= 1, "bad argument");
     double acc = 0.0;
     for (int64_t i = 0; i < n; ++i) { acc += p[i]; cdf[i] = acc; }
     const double tot = cdf[n - 1];
-    for (int64_t i = 0; i < n; ++i) cdf[i] /= tot;
+    host_parallel_for(n, [=](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) cdf[i] /= tot; });
     return DVF_OK;
 }
 

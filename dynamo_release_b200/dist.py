@@ -54,6 +54,8 @@ def gather_rows(t: torch.Tensor, dst: int = 0):
     counts = [int(c.item()) for c in counts]
     # equal-size gather (gloo and nccl both want it): pad every block to the largest row count
     mx = max(counts) if counts else 0
+    if mx == 0:
+        return (t[:0].clone() if rank == dst else None), counts
     pad = t.contiguous()
     if t.shape[0] < mx:
         pad = torch.cat([pad, torch.zeros((mx - t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)], 0)
@@ -64,30 +66,84 @@ def gather_rows(t: torch.Tensor, dst: int = 0):
     return (torch.cat(parts, 0) if rank == dst else None), counts
 
 
-def fit_sharded(X_local, Y_local, M, comm: Comm, seed=0, beta=None, velocity_based_sampling=True, **em):
-    """SparseVFC over row-sharded cells.  The prelude needs the global row order (np.unique semantics,
-    scVectorField.py:403-411): valid rows are gathered on rank 0, which samples the control points and
-    broadcasts them with beta.  Returns (FitState of the local rows, ctrl, idx, beta, local valid index)."""
-    Xd, Yd = dev(X_local), dev(Y_local)
-    valid = prelude.valid_rows(Yd)
-    Xv, Yv = Xd[valid], Yd[valid]
-    Xg, counts = gather_rows(Xv)
-    Yg, _ = gather_rows(Yv)
+class RowServer:
+    """Rows of the row-sharded matrix `Xv` by GLOBAL row number, asked for by rank 0 (a collective: every rank calls
+    fetch() the same number of times; only rank 0 passes indices and gets rows back, in the order it asked)."""
+
+    def __init__(self, Xv: torch.Tensor, counts):
+        self.Xv, self.rank = Xv, dist.get_rank()
+        self.lo = int(sum(counts[:self.rank]))
+        self.hi = self.lo + int(counts[self.rank])
+
+    def fetch(self, gidx=None):
+        dev_ = self.Xv.device
+        k = torch.tensor([gidx.numel() if self.rank == 0 else 0], dtype=torch.int64, device=dev_)
+        dist.broadcast(k, 0)
+        k = int(k.item())
+        g = gidx.to(torch.int64).contiguous() if self.rank == 0 else torch.empty(k, dtype=torch.int64, device=dev_)
+        if k:
+            dist.broadcast(g, 0)
+        sel = torch.nonzero((g >= self.lo) & (g < self.hi), as_tuple=False).reshape(-1)
+        rows, _ = gather_rows(self.Xv[g[sel] - self.lo])
+        pos, _ = gather_rows(sel)
+        if self.rank != 0:
+            return None
+        out = torch.empty((k, self.Xv.shape[1]), dtype=self.Xv.dtype, device=dev_)
+        if k:
+            out[pos] = rows
+        return out
+
+
+def sharded_prelude(Xv, Yv, M, seed=0, beta=None, velocity_based_sampling=True):
+    """Control points and bandwidth of the whole (row-sharded) data set, identical to prelude.run on the
+    concatenated rows (tests/test_dist_cpu.py).  The row order np.unique defines (scVectorField.py:403) needs a
+    global sort, but only of the first coordinate: rank 0 gathers that column and the row speeds (16 bytes per
+    cell instead of 16 D), sorts, asks the owners for the few rows whose first coordinate is tied, samples on the
+    host as the reference does, and asks the owners for the M chosen rows.
+    Returns (ctrl_t, idx (numpy), beta, n_total) on every rank."""
+    rank = dist.get_rank()
+    D = Xv.shape[1]
+    key, counts = gather_rows(Xv[:, 0].contiguous())
+    speed = gather_rows(prelude.row_norms(Yv))[0] if velocity_based_sampling else None
     n_total = int(sum(counts))
-    D = Xd.shape[1]
-    meta = torch.zeros(2, dtype=torch.float64, device=Xd.device)
-    if comm.rank == 0:
-        _, _, _, ctrl, idx, beta = prelude.run(Xg, Yg, M, seed=seed, beta=beta,
-                                               velocity_based_sampling=velocity_based_sampling)
-        meta[0], meta[1] = float(ctrl.shape[0]), beta
-        ctrl_t = dev(ctrl)
-        idx_t = torch.as_tensor(idx, dtype=torch.int64, device=Xd.device)
+    srv = RowServer(Xv, counts)
+    meta = torch.zeros(2, dtype=torch.float64, device=Xv.device)
+    if rank == 0:
+        first = prelude.unique_first(key, srv.fetch)
+        n_u = first.numel()
+        m_eff = min(int(M), n_u)
+        if velocity_based_sampling:
+            idx = prelude.velocity_weighted_choice(prelude.host_f64(speed[first]), m_eff, seed)
+        else:
+            idx = np.random.RandomState(seed=seed).permutation(n_u)[:m_eff]  # scVectorField.py:409-410
+        idx_t = torch.as_tensor(idx, dtype=torch.int64, device=Xv.device)
+        ctrl_t = srv.fetch(first[idx_t])
+        if beta is None:
+            beta = 1.0 / prelude.bandwidth(ctrl_t) ** 2
+        meta[0], meta[1] = float(m_eff), float(beta)
+    else:
+        srv.fetch()
+        srv.fetch()
     dist.broadcast(meta, 0)
     m_eff, beta = int(meta[0].item()), float(meta[1].item())
-    if comm.rank != 0:
-        ctrl_t = torch.empty((m_eff, D), dtype=torch.float64, device=Xd.device)
-        idx_t = torch.empty((m_eff,), dtype=torch.int64, device=Xd.device)
+    if rank != 0:
+        ctrl_t = torch.empty((m_eff, D), dtype=torch.float64, device=Xv.device)
+        idx_t = torch.empty((m_eff,), dtype=torch.int64, device=Xv.device)
     dist.broadcast(ctrl_t, 0)
     dist.broadcast(idx_t, 0)
+    return ctrl_t, idx_t.cpu().numpy(), beta, n_total
+
+
+def fit_sharded(X_local, Y_local, M, comm: Comm, seed=0, beta=None, velocity_based_sampling=True, **em):
+    """SparseVFC over row-sharded cells: sharded_prelude fixes the control points and beta on every rank, then
+    the EM loop runs on the local rows with one allreduce per iteration.
+    Returns (FitState of the local rows, ctrl, idx, beta, local valid index)."""
+    Xd, Yd = dev(X_local), dev(Y_local)
+    valid = prelude.valid_rows(Yd)
+    all_valid = valid.numel() == Yd.shape[0]
+    Xv = Xd if all_valid else Xd[valid]
+    Yv = Yd if all_valid else Yd[valid]
+    ctrl_t, idx, beta, n_total = sharded_prelude(Xv, Yv, M, seed=seed, beta=beta,
+                                                 velocity_based_sampling=velocity_based_sampling)
     st = fit_em(Xv, Yv, ctrl_t, beta, comm=comm.handle, N_total=n_total, **em)
-    return st, ctrl_t, idx_t.cpu().numpy(), beta, valid
+    return st, ctrl_t, idx, beta, valid

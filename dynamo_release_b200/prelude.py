@@ -19,50 +19,107 @@ import numpy as np
 import torch
 
 
+_PINNED = {}
+
+
+def host_f64(t: torch.Tensor) -> np.ndarray:
+    """Device vector -> host NumPy array through a cached pinned staging buffer (a pageable .cpu() of 8M speeds
+    costs more than the sort that produced them)."""
+    if not t.is_cuda:
+        return t.numpy()
+    n = t.numel()
+    buf = _PINNED.get("buf")
+    if buf is None or buf.numel() < n:
+        buf = _PINNED["buf"] = torch.empty(max(n, 1 << 20), dtype=torch.float64, pin_memory=True)
+    buf[:n].copy_(t, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return buf[:n].numpy()
+
+
 def valid_rows(Y: torch.Tensor) -> torch.Tensor:
     """Indices of rows with finite velocity (reference: np.where(np.isfinite(Y.sum(1)))[0])."""
     return torch.nonzero(torch.isfinite(Y.sum(1)), as_tuple=False).reshape(-1)
 
 
-def _lexsort_rows(X: torch.Tensor) -> torch.Tensor:
-    """Stable lexicographic argsort of the rows of X (column 0 most significant)."""
-    n, d = X.shape
-    perm = torch.argsort(X[:, 0], stable=True)
-    if d == 1 or n < 2:
-        return perm
-    k0 = X[perm, 0]
-    tied = torch.zeros(n, dtype=torch.bool, device=X.device)
-    eq = k0[1:] == k0[:-1]
-    tied[1:] |= eq
-    tied[:-1] |= eq
+def unique_first(key0: torch.Tensor, rows_of) -> torch.Tensor:
+    """Indices of the FIRST occurrence of every distinct row, in lexicographic row order (np.unique(axis=0,
+    return_index=True)[1]).  Only column 0 of the rows (`key0`) is sorted; full rows are needed just for the entries
+    whose first coordinate is tied with a neighbour, and `rows_of(index tensor) -> rows` is called exactly once for
+    those (possibly with no indices) -- locally it is an indexing, sharded over ranks it is a small exchange
+    (dist.py), which is why the row matrix itself never has to be gathered."""
+    n = key0.numel()
+    dev_ = key0.device
+    perm = torch.argsort(key0, stable=True)
+    k0 = key0[perm]
+    tied = torch.zeros(n, dtype=torch.bool, device=dev_)
+    if n > 1:
+        eq = k0[1:] == k0[:-1]
+        tied[1:] |= eq
+        tied[:-1] |= eq
     pos = torch.nonzero(tied, as_tuple=False).reshape(-1)
-    if pos.numel() == 0:
-        return perm
-    # refine only the tied positions: LSD stable sorts over columns d-1 .. 1, then by the column-0 group
     sub = perm[pos]
-    grp = torch.cumsum(torch.cat([torch.zeros(1, dtype=torch.int64, device=X.device),
-                                  (k0[pos][1:] != k0[pos][:-1]).to(torch.int64)]), 0)
-    order = torch.arange(sub.numel(), device=X.device)
-    # the entries of `sub` are already in stable (original-index) order inside each group
-    for c in range(d - 1, 0, -1):
-        order = order[torch.argsort(X[sub[order], c], stable=True)]
-    order = order[torch.argsort(grp[order], stable=True)]
-    perm = perm.clone()
-    perm[pos] = sub[order]
-    return perm
+    Xt = rows_of(sub)
+    keep = torch.ones(n, dtype=torch.bool, device=dev_)
+    if pos.numel():
+        kt = k0[pos]
+        grp = torch.cumsum(torch.cat([torch.zeros(1, dtype=torch.int64, device=dev_),
+                                      (kt[1:] != kt[:-1]).to(torch.int64)]), 0)
+        # the entries of `sub` are in stable (original-index) order inside each group: LSD stable sorts over the
+        # columns d-1 .. 1, then by the column-0 group, leave equal rows in original-index order
+        order = torch.arange(sub.numel(), device=dev_)
+        for c in range(Xt.shape[1] - 1, 0, -1):
+            order = order[torch.argsort(Xt[order, c], stable=True)]
+        order = order[torch.argsort(grp[order], stable=True)]
+        perm = perm.clone()
+        perm[pos] = sub[order]
+        Xs, gs = Xt[order], grp[order]
+        dup = (Xs[1:] == Xs[:-1]).all(1) & (gs[1:] == gs[:-1])
+        keep[pos[1:][dup]] = False
+    return perm[torch.nonzero(keep, as_tuple=False).reshape(-1)]
 
 
 def unique_rows(X: torch.Tensor):
     """np.unique(X, axis=0, return_index=True): (sorted unique rows, index of first occurrence)."""
-    perm = _lexsort_rows(X)
-    Xs = X[perm]
     if X.shape[0] == 0:
-        return Xs, perm
-    new = torch.ones(X.shape[0], dtype=torch.bool, device=X.device)
-    new[1:] = (Xs[1:] != Xs[:-1]).any(1)
-    # stable sort => the first element of every run is the smallest original index, as np.unique returns
-    keep = torch.nonzero(new, as_tuple=False).reshape(-1)
-    return Xs[keep], perm[keep]
+        return X, torch.zeros(0, dtype=torch.int64, device=X.device)
+    first = unique_first(X[:, 0].contiguous(), lambda i: X[i])
+    return X[first], first
+
+
+def row_norms(Y: torch.Tensor) -> torch.Tensor:
+    """np.linalg.norm(Y, axis=1) = sqrt(add.reduce(Y*Y, axis=1)) with NumPy's summation order along a contiguous
+    row (pairwise_sum: straight loop below 8 terms, else 8 interleaved partial sums combined as
+    ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)) plus a sequential tail, halves split recursively above 128 terms), done
+    with element-wise column operations so a row's result does not depend on how many rows there are -- a shard
+    and the whole matrix give the same bits."""
+    Yt = Y.T.contiguous()
+    sq = Yt * Yt
+
+    def pairwise(lo, n):
+        if n < 8:
+            res = torch.zeros_like(sq[0])
+            for i in range(n):
+                res = res + sq[lo + i]
+            return res
+        if n <= 128:
+            r = [sq[lo + j].clone() for j in range(8)]
+            i = 8
+            while i < n - (n % 8):
+                for j in range(8):
+                    r[j] += sq[lo + i + j]
+                i += 8
+            res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]))
+            while i < n:
+                res = res + sq[lo + i]
+                i += 1
+            return res
+        n2 = n // 2
+        n2 -= n2 % 8
+        return pairwise(lo, n2) + pairwise(lo + n2, n - n2)
+
+    ss = pairwise(0, Yt.shape[0])
+    # CUDA's double sqrt is correctly rounded like NumPy's; torch's vectorised CPU sqrt is not (CPU = tests only)
+    return torch.sqrt(ss) if ss.is_cuda else torch.from_numpy(np.sqrt(ss.numpy()))
 
 
 def velocity_weighted_choice(speed: np.ndarray, M: int, seed: int) -> np.ndarray:
@@ -78,8 +135,9 @@ def velocity_weighted_choice(speed: np.ndarray, M: int, seed: int) -> np.ndarray
     speed = np.ascontiguousarray(speed, dtype=np.float64)
     n = speed.shape[0]
     rng = np.random.default_rng(seed)
-    p = speed / np.sum(speed)
     lib = _lib.load()
+    p = np.empty(n, dtype=np.float64)
+    _lib.check(lib.dvf_host_scale(speed.ctypes.data_as(C.c_void_p), n, float(np.sum(speed)), p.ctypes.data_as(C.c_void_p)))
     cdf = np.empty(n, dtype=np.float64)
     found = np.zeros(M, dtype=np.int64)
     n_uniq = 0
@@ -124,15 +182,14 @@ def run(X: torch.Tensor, Y: torch.Tensor, M: int, seed: int = 0, beta=None, velo
     all_valid = valid.numel() == Y.shape[0]
     Xv = X if all_valid else X[valid]
     Yv = Y if all_valid else Y[valid]
-    uniq, first = unique_rows(Xv)
-    n_u = uniq.shape[0]
+    first = unique_first(Xv[:, 0].contiguous(), lambda i: Xv[i])
+    n_u = first.numel()
     M = min(int(M), n_u)
     if velocity_based_sampling:
-        speed = torch.linalg.norm(Yv[first], dim=1).cpu().numpy()
-        idx = velocity_weighted_choice(speed, M, seed)
+        idx = velocity_weighted_choice(host_f64(row_norms(Yv)[first]), M, seed)
     else:
         idx = np.random.RandomState(seed=seed).permutation(n_u)[:M]  # scVectorField.py:409-410
-    ctrl_t = uniq[torch.as_tensor(idx, device=X.device)]
+    ctrl_t = Xv[first[torch.as_tensor(idx, device=X.device)]]
     ctrl = ctrl_t.cpu().numpy()
     if beta is None:
         h = bandwidth(ctrl_t)

@@ -171,6 +171,8 @@ int dvf_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch,
  * cdf[i] = (p[0] + ... + p[i]) / total, accumulated strictly left to right in double precision exactly as
  * numpy.cumsum does, so that searchsorted() picks the same cells as the reference.  HOST pointers, no CUDA. */
 int dvf_host_cdf(const double* p, int64_t n, double* cdf);
+/* p[i] = v[i] / total (tools/sampling.py:244, p = |v| / sum|v|); element-wise, split over a few host threads. */
+int dvf_host_scale(const double* v, int64_t n, double total, double* p);
 
 #ifdef __cplusplus
 }

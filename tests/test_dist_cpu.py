@@ -81,3 +81,55 @@ def test_sharded_m_step_algebra_gloo_world2():
     ret = mgr.dict()
     mp.spawn(_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
     assert dict(ret) == {0: "ok", 1: "ok"}
+
+
+def _prelude_case(case):
+    X, V = o.hematopoiesis_like(2503, 9, seed=11 + case)
+    V *= 0.05
+    if case >= 1:
+        # duplicate rows (first occurrence must win), rows that tie on the first coordinate only, across shards
+        X[40] = X[2000]
+        X[1500] = X[7]
+        X[2400] = X[7]
+        X[100, 0] = X[1900, 0]
+        X[101, 0] = X[1900, 0]
+        X[102, :2] = X[1900, :2]
+    if case == 2:
+        X[:, 0] = np.round(X[:, 0], 1)          # heavy ties on the first coordinate
+    return X, V
+
+
+def _prelude_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from dynamo_release_b200 import prelude
+        from dynamo_release_b200.dist import sharded_prelude
+        for case in range(3):
+            X, V = _prelude_case(case)
+            for vbs in (True, False):
+                lo, hi = shard_bounds(len(X), world, rank)
+                ctrl, idx, beta, n_total = sharded_prelude(torch.from_numpy(X[lo:hi].copy()), torch.from_numpy(V[lo:hi].copy()),
+                                                           60, seed=3, velocity_based_sampling=vbs)
+                _, _, _, ctrl1, idx1, beta1 = prelude.run(torch.from_numpy(X.copy()), torch.from_numpy(V.copy()), 60, seed=3,
+                                                          velocity_based_sampling=vbs)
+                assert n_total == len(X)
+                assert np.array_equal(idx, idx1), (case, vbs)
+                assert np.array_equal(ctrl.numpy(), ctrl1), (case, vbs)
+                assert beta == beta1
+                # and both equal the oracle's NumPy prelude (np.unique / Generator.choice themselves)
+                if vbs:
+                    _, _, _, ctrl_o, idx_o, beta_o = o.prelude(X, V, 60, seed=3)
+                    assert np.array_equal(idx, idx_o) and np.array_equal(ctrl.numpy(), ctrl_o)
+                    assert abs(beta - beta_o) <= 1e-13 * beta_o
+        ret[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_prelude_equals_single_process(world):
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_prelude_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
+    assert dict(ret) == {r: "ok" for r in range(world)}
