@@ -15,11 +15,15 @@ from .vf import (  # noqa: F401
     RkhsField,
     RkhsJacobian,
     average_jacobian_by_group,
+    cell_angles,
     compute_acceleration,
     compute_curvature,
     compute_divergence,
     con_K,
     elementwise_jacobian_transformation,
+    jacobian_det,
+    jacobian_det_rkhs,
+    speed,
     subset_jacobian_transformation,
     transform_jacobian,
     vector_field_function,

@@ -49,7 +49,11 @@ SIGNATURES = {
     "dvf_gene_gemm_workspace_bytes": (_i, [_i64, _i, _i, _i, _i, _i, C.POINTER(_sz)]),
     "dvf_gene_transform_gemm": (_i, [_p, _i64, _i, _p, _i, _p, _i, _i, _p, _i, _p, _p, _p, _sz, _p]),
     "dvf_gene_transform_elem": (_i, [_p, _i64, _i, _p, _p, _p, _p]),
+    "dvf_gene_transform_reduce": (_i, [_p, _i64, _i, _p, _i, _p, _i, _i, _i, _p, _p, _i, _p, _p, _sz, _p]),
     "dvf_vector_transform": (_i, [_p, _i64, _i, _p, _i, _p, _p]),
+    "dvf_jacobian_det": (_i, [_p, _i64, _i, _p, _p]),
+    "dvf_cell_angles": (_i, [_p, _p, _i64, _i, _p, _p]),
+    "dvf_row_norms": (_i, [_p, _i64, _i, _p, _p]),
     "dvf_fit_row_width": (_i64, [_i, _i]),
     "dvf_fit_workspace_bytes": (_i, [_i64, _i, _i, C.POINTER(_sz)]),
     "dvf_fit_em": (_i, [_p, _p, _i64, _i64, _i, _p, _i, _d, C.POINTER(EmParams), _p, _p, _p, _p, _p,

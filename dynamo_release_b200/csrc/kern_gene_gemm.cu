@@ -160,21 +160,47 @@ __global__ void k_transpose_q(const double* __restrict__ Q, int G, int D, double
     }
 }
 
-// out_group[g][row] += sum over the chunk's cells with label g of vals[row][cell]; one warp per row, one pass over the
-// row, per-lane per-group partials in shared memory, fixed reduction order (bitwise reproducible, no atomics)
+// out_group[g][row] += sum over the chunk's cells with label g of f(vals[row][cell]); one warp per row, one pass over the
+// row, per-lane per-group partials in shared memory, fixed reduction order (bitwise reproducible, no atomics).
+// The per-cell value f follows rank_jacobian_genes (reference vectorfield/rank_vf.py:483-497) on the float32 entries:
+//   jmax != NULL : a = v / jmax[row]   in float32      (normalize=True, :487-490)
+//   op 0         : f = a                                (mean of J or |J|)
+//   op 1         : f = a * a^T if both are negative, else 0, product rounded to float32   (mode='switch', :492-496;
+//                  a^T is the (r, e) entry, so the matrix must be square: G = Ge = Gr)
+//   op 2         : no groups; out[row] = max(out[row], max over cells of |v|)             (the Jmax of :488)
 __global__ void __launch_bounds__(256) k_gene_group_sum(const float* __restrict__ vals, int64_t ld, int64_t col0, int64_t cells,
                                                         int64_t n_rows, const int32_t* __restrict__ group, int n_groups,
-                                                        double* __restrict__ out_group) {
+                                                        double* __restrict__ out_group, int op, int G,
+                                                        const float* __restrict__ jmax) {
     extern __shared__ double part[];                      // [8 warps][n_groups][32 lanes]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     double* mine = part + (size_t)w * n_groups * 32;
     const int64_t warp0 = (int64_t)blockIdx.x * 8 + w, nwarps = (int64_t)gridDim.x * 8;
     for (int64_t row = warp0; row < n_rows; row += nwarps) {
         const float* v = vals + row * ld + col0;
+        if (op == 2) {
+            float m = 0.f;
+            for (int64_t c = lane; c < cells; c += 32) m = fmaxf(m, fabsf(v[c]));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+            if (lane == 0 && (double)m > out_group[row]) out_group[row] = (double)m;
+            continue;
+        }
+        const int64_t trow = op == 1 ? (row % G) * G + row / G : row;
+        const float* vt = vals + trow * ld + col0;
+        const float sc = jmax ? jmax[row] : 1.f, sct = jmax ? jmax[trow] : 1.f;
         for (int gi = 0; gi < n_groups; ++gi) mine[gi * 32 + lane] = 0.0;
         for (int64_t c = lane; c < cells; c += 32) {
             const int gi = group[c];
-            if (gi >= 0 && gi < n_groups) mine[gi * 32 + lane] += (double)v[c];
+            if (gi < 0 || gi >= n_groups) continue;
+            float a = v[c];
+            if (jmax) a = __fdiv_rn(a, sc);
+            if (op == 1) {
+                float bt = vt[c];
+                if (jmax) bt = __fdiv_rn(bt, sct);
+                a = (a < 0.f && bt < 0.f) ? __fmul_rn(a, bt) : 0.f;
+            }
+            mine[gi * 32 + lane] += (double)a;
         }
         // lane gi ends up with group gi's sum, then the read-modify-writes of up to 32 groups go out together
         for (int g0 = 0; g0 < n_groups; g0 += 32) {
@@ -226,13 +252,14 @@ extern "C" int dvf_gene_gemm_workspace_bytes(int64_t n, int D, int Ge, int Gr, i
     return DVF_OK;
 }
 
-// tensor-core path of dvf_gene_transform (same arguments + workspace)
-extern "C" int dvf_gene_transform_gemm(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr, int Gr,
-                                       int take_abs, const int32_t* group, int n_groups, float* out_full,
-                                       double* out_group_sum, void* ws, size_t ws_bytes, void* stream) {
+static int gene_gemm_run(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr, int Gr,
+                         int take_abs, int op, const float* jmax, const int32_t* group, int n_groups, float* out_full,
+                         double* out_group_sum, void* ws, size_t ws_bytes, void* stream) {
     DVF_ARG(J && Qe && Qr && n >= 0 && D >= 1 && D <= kMaxD && Ge >= 1 && Gr >= 1, "bad argument");
     DVF_ARG(out_full || out_group_sum, "no output requested");
-    DVF_ARG(!out_group_sum || (group && n_groups >= 1), "group labels missing");
+    DVF_ARG(!out_group_sum || op == 2 || (group && n_groups >= 1), "group labels missing");
+    DVF_ARG(op != 1 || Ge == Gr, "the switch product needs a square gene matrix (same effectors and regulators)");
+    if (op == 2) n_groups = 1;
     if (n == 0) return DVF_OK;
     DVF_ARG(((uintptr_t)J & 15) == 0 && (n % 2) == 0, "the tensor-core gene transform needs a 16-byte aligned J and an even number of cells");
     const gg_layout l = gg_make_layout(n, D, Ge, Gr, out_full != nullptr, out_group_sum != nullptr);
@@ -287,10 +314,27 @@ extern "C" int dvf_gene_transform_gemm(const double* J, int64_t n, int D, const 
             DVF_ARG(gs_smem <= 200 * 1024, "n_groups=%d too large for the group-sum kernel (max 100)", n_groups);
             if (gs_smem > 48 * 1024)
                 DVF_CUDA(cudaFuncSetAttribute(k_gene_group_sum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gs_smem));
-            k_gene_group_sum<<<sms * 4, 256, gs_smem, st>>>((const float*)p2.out, p2.ld, p2.out_cell0, nc, (int64_t)Ge * Gr, group + c0,
-                                                      n_groups, out_group_sum);
+            k_gene_group_sum<<<sms * 4, 256, gs_smem, st>>>((const float*)p2.out, p2.ld, p2.out_cell0, nc, (int64_t)Ge * Gr,
+                                                      group ? group + c0 : nullptr, n_groups, out_group_sum, op, Ge, jmax);
             DVF_LAUNCH_CHECK();
         }
     }
     return DVF_OK;
+}
+
+// tensor-core path of dvf_gene_transform (same arguments + workspace)
+extern "C" int dvf_gene_transform_gemm(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr, int Gr,
+                                       int take_abs, const int32_t* group, int n_groups, float* out_full,
+                                       double* out_group_sum, void* ws, size_t ws_bytes, void* stream) {
+    return gene_gemm_run(J, n, D, Qe, Ge, Qr, Gr, take_abs, 0, nullptr, group, n_groups, out_full, out_group_sum, ws, ws_bytes,
+                         stream);
+}
+
+// reductions over cells of the gene-space Jacobian that rank_jacobian_genes consumes, without materialising it
+// (workspace: dvf_gene_gemm_workspace_bytes(n, D, Ge, Gr, full = 0, grouped = 1))
+extern "C" int dvf_gene_transform_reduce(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr, int Gr,
+                                         int take_abs, int op, const float* jmax, const int32_t* group, int n_groups,
+                                         double* out, void* ws, size_t ws_bytes, void* stream) {
+    DVF_ARG(op >= 0 && op <= 2 && out, "bad argument");
+    return gene_gemm_run(J, n, D, Qe, Ge, Qr, Gr, take_abs, op, jmax, group, n_groups, nullptr, out, ws, ws_bytes, stream);
 }

@@ -115,6 +115,35 @@ def div_acc_curv(x, Xc, beta, Cm, formula=2, want=("v", "div", "acc", "acc_norm"
     return out
 
 
+def jacobian_det(J):
+    """K9 -- reference vector_calculus.py:329: det of every cell's Jacobian, J (D, D, n) -> (n,)."""
+    J = dev(J)
+    D, _, n = J.shape
+    out = empty((n,))
+    _lib.check(lib().dvf_jacobian_det(ptr(J), n, D, ptr(out), stream_ptr()))
+    return out
+
+
+def cell_angles(U, V):
+    """K9 -- reference VectorField.py:255-259 / utils.py:1148-1163: signed angle between rows of U and V."""
+    U, V = dev(U), dev(V)
+    n, D = U.shape
+    if V.shape != U.shape:
+        raise ValueError("U and V must have the same shape")
+    out = empty((n,))
+    _lib.check(lib().dvf_cell_angles(ptr(U), ptr(V), n, D, ptr(out), stream_ptr()))
+    return out
+
+
+def row_norms(V):
+    """K9 -- reference vector_calculus.py:192 (speed): Euclidean norm of every row."""
+    V = dev(V)
+    n, D = V.shape
+    out = empty((n,))
+    _lib.check(lib().dvf_row_norms(ptr(V), n, D, ptr(out), stream_ptr()))
+    return out
+
+
 def gene_transform(J, Qe, Qr, take_abs=False, group=None, n_groups=0, full=True):
     """K8 -- reference vectorfield/utils.py:544-554.  J (D, D, n) -> float32 (Ge, Gr, n) and/or group sums."""
     J, Qe, Qr = dev(J), dev(Qe), dev(Qr)
@@ -128,6 +157,38 @@ def gene_transform(J, Qe, Qr, take_abs=False, group=None, n_groups=0, full=True)
     _lib.check(lib().dvf_gene_transform(ptr(J), n, D, ptr(Qe), Ge, ptr(Qr), Gr, int(bool(take_abs)), ptr(group),
                                         int(n_groups), ptr(out), ptr(gsum), stream_ptr()))
     return out, gsum
+
+
+def gene_transform_reduce(J, Qe, Qr, op="sum", take_abs=False, jmax=None, group=None, n_groups=1):
+    """Reductions of the gene-space Jacobian over cells without materialising it (reference rank_vf.py:483-508).
+    op: "sum" (per-group sums), "switch" (per-group sums of J * J^T where both are negative), "max" (max |J|).
+    Returns float64 (n_groups, Ge, Gr) for the sums, (Ge, Gr) for "max"."""
+    import ctypes as C
+    J, Qe, Qr = dev(J), dev(Qe), dev(Qr)
+    D, _, n = J.shape
+    Ge, Gr = Qe.shape[0], Qr.shape[0]
+    code = {"sum": 0, "switch": 1, "max": 2}[op]
+    if group is None:
+        group = torch.zeros(n, dtype=torch.int32, device="cuda")
+    group = dev(group, torch.int32)
+    if n % 2 or J.data_ptr() % 16:
+        # the TMA row pitch (n doubles) must be a multiple of 16 bytes: pad with one cell that belongs to no group
+        Jp = torch.zeros((D, D, n + n % 2), dtype=torch.float64, device="cuda")
+        Jp[:, :, :n] = J
+        group = torch.cat([group, torch.full((n % 2,), -1, dtype=torch.int32, device="cuda")])
+        J, n = Jp, n + n % 2
+    out = torch.zeros((Ge, Gr) if code == 2 else (int(n_groups), Ge, Gr), dtype=torch.float64, device="cuda")
+    if n == 0:
+        return out
+    jm = None if jmax is None else dev(jmax, torch.float32)
+    nbytes = C.c_size_t(0)
+    _lib.check(lib().dvf_gene_gemm_workspace_bytes(n, D, Ge, Gr, 0, 1, C.byref(nbytes)))
+    ws = torch.empty((nbytes.value + 1023) // 8 + 128, dtype=torch.float64, device="cuda")
+    off = (-ws.data_ptr()) % 1024
+    _lib.check(lib().dvf_gene_transform_reduce(ptr(J), n, D, ptr(Qe), Ge, ptr(Qr), Gr, int(bool(take_abs)), code, ptr(jm),
+                                               ptr(group), int(n_groups), ptr(out), ws.data_ptr() + off, nbytes.value,
+                                               stream_ptr()))
+    return out
 
 
 def gene_transform_elem(J, qe, qr):

@@ -12,7 +12,7 @@ import numpy as np
 import torch
 
 from . import kernels
-from .device import dev, host
+from .device import dev, empty, host
 
 
 def _out(t, device_out):
@@ -226,3 +226,41 @@ def average_jacobian_by_group(Js, Qi, Qj, group_labels, n_groups, take_abs=False
                                      group=lab, n_groups=int(n_groups), full=False)
     cnt = np.bincount(lab, minlength=int(n_groups)).astype(np.float64)
     return host(gsum) / np.maximum(cnt, 1.0)[:, None, None]
+
+
+# ------------------------------------------------------------------------------------------------------
+# per-cell post-processing the reference's adata wrappers do in Python loops
+# ------------------------------------------------------------------------------------------------------
+def jacobian_det(Js, device_out=False):
+    """det of every cell's Jacobian, Js (D, D, n) -> (n,): the list comprehension of np.linalg.det at
+    reference vectorfield/vector_calculus.py:329."""
+    Jd = dev(Js)
+    if Jd.dim() == 2:
+        Jd = Jd[:, :, None]
+    return _out(kernels.jacobian_det(Jd.contiguous()), device_out)
+
+
+def jacobian_det_rkhs(x, vf_dict, device_out=False, chunk=131072):
+    """det J(x_c) for every row of x straight from the fitted field: J is produced and consumed on the device one
+    chunk of cells at a time, so the (D, D, n) array never exists (vector_calculus.py:265-266 + :329)."""
+    Xc, beta, C = _vf_parts(vf_dict)
+    x2, _ = _as2d(x)
+    xd = dev(x2)
+    n = xd.shape[0]
+    out = empty((n,))
+    for lo in range(0, n, int(chunk)):
+        hi = min(n, lo + int(chunk))
+        out[lo:hi] = kernels.jacobian_det(kernels.jacobian(xd[lo:hi], Xc, beta, C))
+    return _out(out, device_out)
+
+
+def cell_angles(U, V, device_out=False):
+    """Signed angle between the observed (U) and fitted (V) velocity of every cell: the per-cell loop over
+    `angle` at reference vectorfield/VectorField.py:255-259 (angle: vectorfield/utils.py:1148-1163)."""
+    return _out(kernels.cell_angles(np.asarray(U, dtype=np.float64) if not torch.is_tensor(U) else U,
+                                    np.asarray(V, dtype=np.float64) if not torch.is_tensor(V) else V), device_out)
+
+
+def speed(V, device_out=False):
+    """|v| per cell: reference vectorfield/vector_calculus.py:192."""
+    return _out(kernels.row_norms(V), device_out)

@@ -81,12 +81,35 @@ int dvf_gene_gemm_workspace_bytes(int64_t n, int D, int Ge, int Gr, int full, in
 int dvf_gene_transform_gemm(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr, int Gr,
                             int take_abs, const int32_t* group, int n_groups, float* out_full,
                             double* out_group_sum, void* ws, size_t ws_bytes, void* stream);
+/* Reductions over cells of the float32 gene-space Jacobian that rank_jacobian_genes consumes
+ * (vectorfield/rank_vf.py:483-508), without materialising the (Ge, Gr, n) array.  Per-cell value, in the reference's
+ * order: |.| if take_abs (:484-485); divided in float32 by jmax[e][r] if jmax != NULL (normalize, :487-490);
+ *   op 0: out[g][e][r] += value over the cells with group[c] == g        (means: :498-508, utils.py:557-582)
+ *   op 1: out[g][e][r] += value * value^T where both are negative        (mode='switch', :492-496; needs Ge == Gr)
+ *   op 2: out[e][r] = max(out[e][r], max over cells |value|)             (the Jmax of :488; group ignored)
+ * `out` is accumulated into (zero it first); workspace = dvf_gene_gemm_workspace_bytes(n, D, Ge, Gr, 0, 1).
+ * n must be even and J 16-byte aligned (TMA row pitch). */
+int dvf_gene_transform_reduce(const double* J, int64_t n, int D, const double* Qe, int Ge, const double* Qr, int Gr,
+                              int take_abs, int op, const float* jmax, const int32_t* group, int n_groups,
+                              double* out, void* ws, size_t ws_bytes, void* stream);
 int dvf_gene_transform_elem(const double* J, int64_t n, int D, const double* qe, const double* qr,
                             double* out_elem, void* stream);
 
 /* K16: out (n x G) = V (n x D) Q^T, Q is (G x D).   replaces vectorfield/utils.py:311-326. */
 int dvf_vector_transform(const double* V, int64_t n, int D, const double* Q, int G, double* out,
                          void* stream);
+
+/* ---- K9: per-cell post-processing (Python loops over cells in the reference) ---------------
+ * dvf_jacobian_det: det[c] = det(J[:, :, c]), J is (D, D, n) cell-fastest.  replaces the per-cell np.linalg.det of
+ *   vectorfield/vector_calculus.py:329 (LU with partial pivoting, pivot rule and reciprocal scaling of LAPACK
+ *   dgetf2; the product of the pivots is accumulated with a separate exponent).
+ * dvf_cell_angles: out[c] = angle(U[c], V[c]) of vectorfield/utils.py:1148-1163 (called per cell at
+ *   vectorfield/VectorField.py:255-259): sign * arccos(clip(u.v / |u||v|)), sign = -sign of the 2 x 2 determinant
+ *   of the last two unit-vector components (1 if it is zero), NaN if either norm is zero.  U, V are n x D.
+ * dvf_row_norms: out[c] = |V[c]|  (vector_calculus.py:192, `speed`). */
+int dvf_jacobian_det(const double* J, int64_t n, int D, double* det, void* stream);
+int dvf_cell_angles(const double* U, const double* V, int64_t n, int D, double* out, void* stream);
+int dvf_row_norms(const double* V, int64_t n, int D, double* out, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * SparseVFC EM fit (vectorfield/scVectorField.py:417-497; Gaussian kernel branch)

@@ -275,6 +275,36 @@ def to_gene_space(V, Q):
 
 
 # --------------------------------------------------------------------------------------------
+# per-cell post-processing
+# --------------------------------------------------------------------------------------------
+def jacobian_det(Js):
+    """vectorfield/vector_calculus.py:329: np.linalg.det of every cell's Jacobian."""
+    Js = np.atleast_3d(Js)
+    return np.array([np.linalg.det(Js[:, :, i]) for i in range(Js.shape[2])])
+
+
+def vector_angle(v1, v2):
+    """vectorfield/utils.py:1148-1173 (angle / unit_vector)."""
+    n1, n2 = np.linalg.norm(v1), np.linalg.norm(v2)
+    if n1 == 0 or n2 == 0:
+        return np.nan
+    u1, u2 = v1 / n1, v2 / n2
+    minor = np.linalg.det(np.stack((u1[-2:], u2[-2:])))
+    sign = 1 if minor == 0 else -np.sign(minor)
+    return sign * np.arccos(min(max(np.dot(u1, u2), -1.0), 1.0))
+
+
+def cell_angles(U, V):
+    """vectorfield/VectorField.py:255-259: angle between observed and fitted velocity, per cell."""
+    return np.array([vector_angle(u.astype("float64"), v.astype("float64")) for u, v in zip(U, V)])
+
+
+def speed(V):
+    """vectorfield/vector_calculus.py:192."""
+    return np.array([np.linalg.norm(i) for i in V])
+
+
+# --------------------------------------------------------------------------------------------
 # normalisation (scVectorField.py:64-96, 138-182)
 # --------------------------------------------------------------------------------------------
 def normalise(X, V, fix_velocity=True):

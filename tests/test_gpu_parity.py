@@ -249,6 +249,134 @@ def test_jacobian_gemm_form_chunks_and_pool_entry(pkg):
     assert bool(torch.isfinite(J).all())
 
 
+def test_per_cell_postprocessing(pkg):
+    """K9: determinant, observed-vs-fitted angle and speed per cell against the oracle's
+    restatement of the reference loops (vector_calculus.py:329, VectorField.py:255-259, vector_calculus.py:192)."""
+    rng = np.random.default_rng(5)
+    # well-conditioned random matrices, all supported shapes incl. ragged cell counts and the block boundaries
+    for D, n in ((1, 7), (2, 1001), (3, 64), (17, 333), (30, 4099), (33, 50), (50, 257), (64, 130)):
+        J = rng.standard_normal((D, D, n)) + 0.5 * np.eye(D)[:, :, None]
+        got, ref = pkg.jacobian_det(J), o.jacobian_det(J)
+        assert got.shape == (n,)
+        assert np.max(np.abs(got - ref) / np.abs(ref)) < 1e-11, (D, n)
+    # pivoting / sign / scaling corner cases
+    D = 6
+    J = rng.standard_normal((D, D, 8))
+    J[:, :, 0] = np.eye(D)[[1, 0, 2, 3, 5, 4]]                   # permutation: det = +1 (two swaps)
+    J[:, :, 1] = np.eye(D)[[1, 0, 2, 3, 4, 5]]                   # one swap: det = -1
+    J[:, 2, 2] = 0.0                                             # zero column: singular
+    J[:, :, 3] = np.diag([1e200, 1e200, 1e-200, 1e-200, 3.0, -2.0])   # partial products overflow, result does not
+    J[:, :, 4] = J[:, :, 5] * 1e-40                              # tiny entries
+    got, ref = pkg.jacobian_det(J), o.jacobian_det(J)
+    assert got[0] == 1.0 and got[1] == -1.0 and got[2] == 0.0
+    assert abs(got[3] - (-6.0)) < 1e-12                          # numpy's exp(log) route gives -6 (1 +- 1e-13)
+    ok = np.abs(ref) > 0
+    assert np.max(np.abs(got[ok] - ref[ok]) / np.abs(ref[ok])) < 1e-10
+    # the fitted field's Jacobians (ill-conditioned: the field lives near a low-dimensional manifold), compared
+    # within the perturbation bound of a determinant, n * eps * cond
+    g = Golden("hema_n2000_d30_m100")
+    vf, xs = g.vf(), g.X[g["calc_cells"]]
+    Js = pkg.Jacobian_rkhs_gaussian(xs, vf)
+    got, ref = pkg.jacobian_det(Js), o.jacobian_det(Js)
+    cond = np.array([np.linalg.cond(Js[:, :, i]) for i in range(Js.shape[2])])
+    assert np.all(np.abs(got - ref) <= 100 * xs.shape[1] * 2.3e-16 * cond * np.abs(ref) + 1e-300)
+    assert np.array_equal(np.sign(got), np.sign(ref))
+    fused = pkg.jacobian_det_rkhs(xs, vf, chunk=37)
+    assert np.array_equal(fused, got)
+
+    # angles and speed
+    for D in (2, 3, 30, 50):
+        U, V = rng.standard_normal((2003, D)), rng.standard_normal((2003, D))
+        V[:50] = U[:50] * rng.random((50, 1)) * 3                # parallel
+        V[50:100] = -U[50:100]                                   # anti-parallel
+        V[100:120] = U[100:120] + 1e-9 * rng.standard_normal((20, D))
+        U[200] = 0.0
+        V[201] = 0.0
+        got, ref = pkg.cell_angles(U, V), o.cell_angles(U, V)
+        assert np.isnan(got[200]) and np.isnan(got[201]) and np.array_equal(np.isnan(got), np.isnan(ref))
+        fin = ~np.isnan(ref)
+        # arccos is ill-conditioned at +-1: a 1-ulp change of the dot product moves the angle by eps / sin(angle)
+        tol = 1e-13 + 1e-15 / np.maximum(np.abs(np.sin(ref[fin])), 1e-8)
+        gen = np.ones(len(U), bool)
+        gen[:120] = False                                        # (anti)parallel rows: the sign is 0/0 noise
+        assert np.all(np.abs(np.abs(got[fin]) - np.abs(ref[fin])) <= tol), D
+        assert np.array_equal(np.sign(got[fin & gen]), np.sign(ref[fin & gen])), D
+        assert rel(pkg.speed(V), o.speed(V)) < 1e-15
+
+
+def test_rank_tables_match_reference(pkg):
+    """rank_jacobian_genes tables (all modes x abs x normalize x groups x exclude_diagonal) against the tables the
+    executed reference produced (oracle/gen_golden_post.py): gene orders exact -- a swap is tolerated only between
+    entries whose reference values are closer than the float32 accumulation noise -- values to 5e-6."""
+    import os
+    from dynamo_release_b200 import rank
+    from oracle.gen_golden_post import RANK_CASES, rank_case_key
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "post", "rank_tables.npz"))
+    genes, Q, Js, labels = z["genes"], z["Q"], z["Js"], z["labels"]
+    name_to_i = {n: i for i, n in enumerate(genes)}
+    n_swaps = n_exact = n_entries = 0
+
+    def check(idx, val, ridx, rval, what):
+        nonlocal n_swaps, n_exact, n_entries
+        idx, ridx = np.asarray(idx), np.asarray(ridx)
+        assert idx.shape == ridx.shape, what
+        scale = np.nanmax(np.abs(rval)) if np.isfinite(np.nanmax(np.abs(rval))) else 1.0
+        fin = np.isfinite(rval)
+        assert np.array_equal(fin, np.isfinite(val)), what
+        assert np.all(np.abs(np.asarray(val)[fin] - rval[fin]) <= 5e-6 * scale), what
+        bad = np.nonzero((idx != ridx).reshape(len(rval), -1).any(1))[0]
+        n_entries += len(rval)
+        for b in bad:   # a disagreement must be a tie or a near-tie in the reference's own values
+            if (rval == rval[b]).sum() > 1:
+                n_exact += 1            # e.g. the zeros of mode='switch': any order is a valid argsort
+                continue
+            near = np.abs(rval - rval[b]) <= 2e-6 * scale
+            assert near.sum() > 1, (what, b)
+            n_swaps += 1
+
+    for case in RANK_CASES:
+        mode, ab, norm, grouped, exd = case
+        key = rank_case_key(*case)
+        tab = rank.rank_jacobian_genes(Js, Q, Q, genes, genes, groups=labels if grouped else None, abs=ab, mode=mode,
+                                       exclude_diagonal=exd, normalize=norm)
+        groups = [str(x) for x in z[key + "|groups"]]
+        if isinstance(tab, dict):
+            assert [str(k) for k in tab.keys()] == groups, key
+            for k, df in tab.items():
+                ridx, rval = z["%s|%s|idx" % (key, k)], z["%s|%s|val" % (key, k)]
+                for i, item in enumerate(genes):
+                    check([name_to_i[x] for x in df[item]], df[item + "_values"].to_numpy(), ridx[i], rval[i], (key, k, item))
+        else:
+            cols = [str(c) for c in tab.columns if not str(c).endswith("_values")]
+            assert cols == groups, key
+            for c in cols:
+                ridx, rval = z["%s|%s|idx" % (key, c)], z["%s|%s|val" % (key, c)]
+                if mode in ("int", "switch"):
+                    got = [[name_to_i[a], name_to_i[b]] for a, b in (s.split(" - ") for s in tab[c])]
+                else:
+                    got = [name_to_i[x] for x in tab[c]]
+                check(got, tab[c + "_values"].to_numpy(dtype=np.float64), ridx, rval, (key, c))
+    print("rank tables: %d cases, %d entries, %d positions inside exact ties, %d near-tie swaps"
+          % (len(RANK_CASES), n_entries, n_exact, n_swaps))
+    assert n_swaps <= 0.002 * n_entries
+    # the fused means equal the materialised route: float32 transform -> mean in float64
+    Jg = pkg.transform_jacobian(Js, Q, Q).astype(np.float64)
+    keys, Jm = rank.jacobian_gene_means(Js, Q, Q, groups=labels)
+    for gi, k in enumerate(keys):
+        assert rel(_np(Jm[gi]), Jg[:, :, labels == k].mean(2)) < 1e-14
+    assert keys == list(dict.fromkeys(labels.tolist()))
+    # odd cell count and a large gene set through the same entry point
+    rng = np.random.default_rng(3)
+    J2 = rng.standard_normal((20, 20, 333))
+    Q2 = rng.standard_normal((150, 20))
+    lab2 = rng.integers(0, 4, 333)
+    keys2, Jm2 = rank.jacobian_gene_means(J2, Q2, Q2, groups=lab2, switch=True)
+    Jg2 = o.gene_jacobian(J2, Q2, Q2)
+    sw = (Jg2 * Jg2.transpose(1, 0, 2)) * (Jg2 < 0) * (Jg2.transpose(1, 0, 2) < 0)
+    for gi, k in enumerate(keys2):
+        assert rel(_np(Jm2[gi]), sw[:, :, lab2 == k].astype(np.float64).mean(2)) < 1e-6
+
+
 def test_edge_cases(pkg):
     rng = np.random.default_rng(1)
     vf = {"X_ctrl": rng.normal(size=(7, 3)), "beta": 0.3, "C": rng.normal(size=(7, 3))}

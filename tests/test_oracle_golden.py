@@ -51,3 +51,20 @@ def test_oracle_calculus_matches_reference(name):
     assert np.array_equal(o.gene_jacobian(Jg, Q[: ng // 2], Q[ng // 3:]), g["gene_full"])
     assert rel(o.gene_jacobian_element(Jg, Q[1], Q[5]), g["gene_elem"]) < 1e-13
     assert rel(o.to_gene_space(g["calc_acc_mat"], Q), g["gene_vec"]) < 1e-13
+
+
+def test_oracle_postprocessing_matches_reference():
+    """Per-cell angle / speed / determinant restatements against the executed reference (oracle/gen_golden_post.py)."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "post", "post_cells.npz"))
+    for D in (2, 3, 30):
+        U, V = z["U_%d" % D], z["V_%d" % D]
+        a = o.cell_angles(U, V)
+        assert np.array_equal(np.isnan(a), np.isnan(z["angle_%d" % D]))
+        assert np.array_equal(a[~np.isnan(a)], z["angle_%d" % D][~np.isnan(a)])
+        assert np.array_equal(o.speed(V), z["speed_%d" % D])
+    g = Golden("hema_n2000_d30_m100")
+    Js = o.jacobian(g.X[z["det_cells"]], g.vf())
+    # the Jacobians agree to 1e-13; a determinant moves by n * eps * cond relative to that
+    cond = np.array([np.linalg.cond(Js[:, :, i]) for i in range(Js.shape[2])])
+    assert np.all(np.abs(o.jacobian_det(Js) - z["det"]) <= 1e-12 * cond * np.abs(z["det"]))
