@@ -54,6 +54,7 @@ __host__ __device__ inline int gv_ks(int v) { return v == GV_FULL ? 1 : v == GV_
 // relative cost of one 32-cell step (DMMA count x a penalty for the smaller shapes, calibrated on B200 with
 // DVF_GRAM_ONLY, tools/gram_tune.py)
 static double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.1, 128.0 * 1.05, 64.0 * 1.1, 48.0 * 1.15, 32.0 * 1.25, 16.0 * 1.6};
+static double g_diag_factor = 0.78;
 static int g_force_G = 0, g_sb = 64, g_lag = 0, g_only = -1, g_debug = 0;   // sb, lag: measured on B200
 static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not part of the ABI
     static bool done = false;
@@ -63,13 +64,14 @@ static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not p
         sscanf(e, "%lf,%lf,%lf,%lf,%lf,%lf,%lf", &kVarCost[0], &kVarCost[1], &kVarCost[2], &kVarCost[3], &kVarCost[4],
                &kVarCost[5], &kVarCost[6]);
     if (const char* e = getenv("DVF_GRAM_G")) g_force_G = atoi(e);
+    if (const char* e = getenv("DVF_GRAM_DIAG")) g_diag_factor = atof(e);
     if (const char* e = getenv("DVF_GRAM_SB")) g_sb = std::max(1, atoi(e));
     if (const char* e = getenv("DVF_GRAM_LAG")) g_lag = atoi(e);       // blocks a producer may run ahead of its group
     if (const char* e = getenv("DVF_GRAM_ONLY")) g_only = atoi(e);     // timing experiments: keep one tile variant
     if (const char* e = getenv("DVF_GRAM_DEBUG")) g_debug = atoi(e);
 }
 
-struct gram_tile { int variant, row0, col0, pad0, pad1; };
+struct gram_tile { int variant, row0, col0, diag, pad1; };   // diag: 64 x 64 tile on the diagonal (upper-right 32 x 32 unused)
 struct gr_ring { int stage; unsigned phase; };
 __device__ __forceinline__ void gr_advance(gr_ring& r) { if (++r.stage == GR_STAGES) { r.stage = 0; r.phase ^= 1u; } }
 
@@ -79,7 +81,7 @@ __device__ __forceinline__ void gr_advance(gr_ring& r) { if (++r.stage == GR_STA
 // k-step s of a stage uses the cells r(s, t) = 8 (s / 2) + 2 t + (s & 1), t = 0..3: the 32 lanes of a fragment load
 // (8 columns x 4 cells) then touch every bank exactly twice (2 wavefronts, the minimum for 256 bytes).
 template <int V>
-__device__ __forceinline__ void gram_consume(int n_steps, double* __restrict__ out, bool accumulate,
+__device__ __forceinline__ void gram_consume(int n_steps, double* __restrict__ out, bool accumulate, bool diag,
                                              const unsigned char* ring, uint64_t* full, uint64_t* empty, gr_ring& rs) {
     using gv = gvar<V>;
     constexpr int RT = gv::RT, CT = gv::CT, WJ = gv::WJ, KS = gv::KS;
@@ -87,8 +89,21 @@ __device__ __forceinline__ void gram_consume(int n_steps, double* __restrict__ o
     constexpr int SPW = (GR_KC / 4) / KS;                 // k-steps per warp and stage (8, 4 or 2)
     constexpr int POS = gv::WI * WJ;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int kg = warp / POS, pos = warp % POS, wi = pos / WJ, wj = pos % WJ;
+    // 64 x 64 tiles rotate the positions through the k-groups, so that the four warps of one position sit on four
+    // different schedulers (warp % 4): a diagonal tile then idles one warp per scheduler, not one whole scheduler
+    const int kg = warp / POS, pos = (V == GV_HALF) ? (warp + kg) % POS : warp % POS, wi = pos / WJ, wj = pos % WJ;
     out += kg * (TR * TC);
+    if (V == GV_HALF && diag && wi < wj) {
+        // the 32 x 32 block above the diagonal is never read: only keep the ring protocol going (a warp may arrive
+        // on `empty` for a stage once per fill, so it still waits for every fill)
+        for (int step = 0; step < n_steps; ++step) {
+            mbar_wait(&full[rs.stage], rs.phase);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[rs.stage]);
+            gr_advance(rs);
+        }
+        return;
+    }
 
     double acc[RT][CT][2];
 #pragma unroll
@@ -234,13 +249,13 @@ __global__ void __launch_bounds__(GR_THREADS, 1) k_gram(const __grid_constant__ 
         const gram_tile tl = tiles[ti];
         double* out = slots + ((size_t)grp * n_tiles + ti) * GR_SLOT;
         switch (tl.variant) {
-            case GV_FULL: gram_consume<GV_FULL>(n, out, acc, ring, full, empty, rs); break;
-            case GV_HALF: gram_consume<GV_HALF>(n, out, acc, ring, full, empty, rs); break;
-            case GV_S8:   gram_consume<GV_S8>(n, out, acc, ring, full, empty, rs); break;
-            case GV_S4:   gram_consume<GV_S4>(n, out, acc, ring, full, empty, rs); break;
-            case GV_S3:   gram_consume<GV_S3>(n, out, acc, ring, full, empty, rs); break;
-            case GV_S2:   gram_consume<GV_S2>(n, out, acc, ring, full, empty, rs); break;
-            default:      gram_consume<GV_S1>(n, out, acc, ring, full, empty, rs); break;
+            case GV_FULL: gram_consume<GV_FULL>(n, out, acc, tl.diag != 0, ring, full, empty, rs); break;
+            case GV_HALF: gram_consume<GV_HALF>(n, out, acc, tl.diag != 0, ring, full, empty, rs); break;
+            case GV_S8:   gram_consume<GV_S8>(n, out, acc, tl.diag != 0, ring, full, empty, rs); break;
+            case GV_S4:   gram_consume<GV_S4>(n, out, acc, tl.diag != 0, ring, full, empty, rs); break;
+            case GV_S3:   gram_consume<GV_S3>(n, out, acc, tl.diag != 0, ring, full, empty, rs); break;
+            case GV_S2:   gram_consume<GV_S2>(n, out, acc, tl.diag != 0, ring, full, empty, rs); break;
+            default:      gram_consume<GV_S1>(n, out, acc, tl.diag != 0, ring, full, empty, rs); break;
         }
     };
     if (single) {
@@ -265,6 +280,7 @@ __global__ void __launch_bounds__(256) k_gram_reduce(const gram_tile* __restrict
     const int TR = gv_rows(tl.variant), TC = gv_cols(tl.variant), KS = gv_ks(tl.variant);
     const double* src = slots + (size_t)blockIdx.x * GR_SLOT;
     for (int e = blockIdx.y * 256 + threadIdx.x; e < TR * TC; e += gridDim.y * 256) {
+        if (tl.diag && e / TC < 32 && e % TC >= 32) continue;        // not computed (above the diagonal)
         double sum = 0.0;
         for (int gi = 0; gi < n_groups; ++gi)
             for (int k = 0; k < KS; ++k) sum += src[(size_t)gi * n_tiles * GR_SLOT + k * TR * TC + e];
@@ -286,10 +302,13 @@ struct gram_host_plan {
     int n_groups = 1;
 };
 
+// a diagonal 64 x 64 tile runs 12 of its 16 warps
+static double tile_cost(const gram_tile& tl) { return kVarCost[tl.variant] * (tl.diag ? g_diag_factor : 1.0); }
+
 static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& hp) {
     read_tuning_env();
     const int units = (M + D + 7) / 8, nfull = units / 16, rt = units % 16;
-    auto add = [&](int v, int r0, int c0) { hp.tiles.push_back(gram_tile{v, r0, c0, 0, 0}); };
+    auto add = [&](int v, int r0, int c0) { hp.tiles.push_back(gram_tile{v, r0, c0, (v == GV_HALF && r0 == c0) ? 1 : 0, 0}); };
     for (int s = 0; s < nfull; ++s) {
         for (int jb = 0; jb < s; ++jb) add(GV_FULL, 128 * s, 128 * jb);
         add(GV_HALF, 128 * s, 128 * s);
@@ -314,10 +333,10 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
     std::vector<int> by_cost(nt);
     for (int i = 0; i < nt; ++i) by_cost[i] = i;
     std::stable_sort(by_cost.begin(), by_cost.end(), [&](int a, int b) {
-        return kVarCost[hp.tiles[a].variant] > kVarCost[hp.tiles[b].variant];
+        return tile_cost(hp.tiles[a]) > tile_cost(hp.tiles[b]);
     });
     double total = 0.0;
-    for (auto& tl : hp.tiles) total += kVarCost[tl.variant];
+    for (auto& tl : hp.tiles) total += tile_cost(tl);
     // choose the number of bundles G (LPT bin packing) that maximises
     //   total / (G * max_bin)  x  (G * groups) / n_sms ,  groups = min(n_sms / G, n_steps)
     double best_eff = -1.0;
@@ -332,7 +351,7 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
         std::vector<int> assign(nt, 0);
         for (int id : by_cost) {
             int k = (int)(std::min_element(bin.begin(), bin.end()) - bin.begin());
-            bin[k] += kVarCost[hp.tiles[id].variant];
+            bin[k] += tile_cost(hp.tiles[id]);
             assign[id] = k;
         }
         const double mx = *std::max_element(bin.begin(), bin.end());
