@@ -315,7 +315,7 @@ def run_ours(a):
                           for i, k in enumerate(["prelude", "fit", "jacobian", "div_acc_curv"])},
             "e2e": e2e,
             "gpu_launches": int(launches.value),
-            "roofline": {"bound": "tensor", "kernel": "k_gram (weighted Gram + RHS, FP64 DMMA m8n8k4 fed by TMA) + k_gram_reduce",
+            "roofline": {"bound": "tensor", "kernel": "k_gram_parts (k_gram for many tiles): weighted Gram + RHS, FP64 DMMA m8n8k4 fed by TMA, + its reduce kernel",
                          "achieved": achieved, "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s",
                          "frac": achieved / FP64_PEAK_TFLOPS,
                          # dram__bytes_read.sum + dram__bytes_write.sum of one k_gram launch at the default workload from

@@ -16,7 +16,8 @@ enum { RED_SUM_PR2 = 0, RED_SUM_P = 1, RED_SUM_PC = 2, RED_NCORR = 3, RED_COUNT 
 
 struct gram_plan {
     int ldg, n_ctas, n_tiles, n_bundles, n_groups, sb, lag;
-    size_t off_tiles, off_boff, off_btiles, off_progress, off_pclamp, off_slots, scratch_bytes;
+    int use_parts, n_parts, sb_parts, n_counters;     // "parts" schedule (kern_gram.cu): one tile part per CTA
+    size_t off_tiles, off_boff, off_btiles, off_progress, off_parts, off_poff, off_pclamp, off_slots, scratch_bytes;
 };
 gram_plan make_gram_plan(int64_t N, int D, int M);
 int gram_prepare(const gram_plan& pl, int64_t N, int D, int M, void* scratch, cudaStream_t st);

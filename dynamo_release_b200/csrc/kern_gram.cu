@@ -55,6 +55,7 @@ __host__ __device__ inline int gv_ks(int v) { return v == GV_FULL ? 1 : v == GV_
 // DVF_GRAM_ONLY, tools/gram_tune.py)
 static double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.1, 128.0 * 1.05, 64.0 * 1.1, 48.0 * 1.15, 32.0 * 1.25, 16.0 * 1.6};
 static double g_diag_factor = 0.78;
+static int g_parts = -1, g_sb_parts = 512;   // -1: planner decides, 0: bundles only, 1: parts whenever possible
 static int g_force_G = 0, g_sb = 64, g_lag = 0, g_only = -1, g_debug = 0;   // sb, lag: measured on B200
 static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not part of the ABI
     static bool done = false;
@@ -65,6 +66,8 @@ static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not p
                &kVarCost[5], &kVarCost[6]);
     if (const char* e = getenv("DVF_GRAM_G")) g_force_G = atoi(e);
     if (const char* e = getenv("DVF_GRAM_DIAG")) g_diag_factor = atof(e);
+    if (const char* e = getenv("DVF_GRAM_PARTS")) g_parts = atoi(e);
+    if (const char* e = getenv("DVF_GRAM_SBP")) g_sb_parts = std::max(8, atoi(e));
     if (const char* e = getenv("DVF_GRAM_SB")) g_sb = std::max(1, atoi(e));
     if (const char* e = getenv("DVF_GRAM_LAG")) g_lag = atoi(e);       // blocks a producer may run ahead of its group
     if (const char* e = getenv("DVF_GRAM_ONLY")) g_only = atoi(e);     // timing experiments: keep one tile variant
@@ -289,6 +292,93 @@ __global__ void __launch_bounds__(256) k_gram_reduce(const gram_tile* __restrict
     }
 }
 
+// ---- "parts" schedule: one CTA = one part of one tile for the whole launch ---------------------------------------
+// Tile t is cut into p_t parts (p_t ~ cost_t, sum p_t <= #SMs): inside every block of `sb` steps, part k takes the
+// steps [len k / p_t, len (k+1) / p_t).  All CTAs sweep the blocks together (a counter per block, `lag` blocks of
+// slack), so a block of rows is fetched from HBM once and served from L2 to every tile that needs it, and no CTA ever
+// swaps accumulators: its partial tile lives in registers from the first step to the last.
+struct gram_part { int tile, k, p, pad; };
+
+__device__ __forceinline__ void gp_range(int b, int sb, int n_steps, int k, int p, int& lo, int& hi) {
+    const int b_lo = b * sb, len = min(sb, n_steps - b_lo);
+    lo = b_lo + (int)((int64_t)len * k / p);
+    hi = b_lo + (int)((int64_t)len * (k + 1) / p);
+}
+
+__global__ void __launch_bounds__(GR_THREADS, 1) k_gram_parts(const __grid_constant__ CUtensorMap mapUY,
+                                                              const __grid_constant__ CUtensorMap mapP, int64_t N,
+                                                              const gram_tile* __restrict__ tiles,
+                                                              const gram_part* __restrict__ parts, int sb, int lag,
+                                                              double* __restrict__ slots, int* __restrict__ counters,
+                                                              const int* __restrict__ done) {
+    if (done && *done) return;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned char* ring = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint64_t* full = reinterpret_cast<uint64_t*>(ring + GR_STAGES * GR_STAGE_B);
+    uint64_t* empty = full + GR_STAGES;
+    if (threadIdx.x == 0) {
+        for (int q = 0; q < GR_STAGES; ++q) { mbar_init(&full[q], 1); mbar_init(&empty[q], GR_CWARPS); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const gram_part pt = parts[blockIdx.x];
+    const gram_tile tl = tiles[pt.tile];
+    const int n_steps = (int)((N + GR_KC - 1) / GR_KC), n_blocks = (n_steps + sb - 1) / sb;
+    gr_ring rs{0, 0u};
+    const int warp = threadIdx.x >> 5;
+
+    if (warp == GR_CWARPS) {
+        if ((threadIdx.x & 31) != 0) return;
+        const int n_ctas = (int)gridDim.x;
+        for (int b = 0; b < n_blocks; ++b) {
+            atomicAdd(counters + b, 1);                       // this CTA starts block b
+            if (b - lag >= 0)
+                for (int spin = 0; spin < (1 << 20) && ld_volatile_i32(counters + b - lag) < n_ctas; ++spin) {}
+            int lo, hi;
+            gp_range(b, sb, n_steps, pt.k, pt.p, lo, hi);
+            gram_produce(&mapUY, &mapP, tl, lo, hi, ring, full, empty, rs);
+        }
+        return;
+    }
+    int total = 0;
+    for (int b = 0; b < n_blocks; ++b) {
+        int lo, hi;
+        gp_range(b, sb, n_steps, pt.k, pt.p, lo, hi);
+        total += hi - lo;
+    }
+    double* out = slots + (size_t)blockIdx.x * GR_SLOT;
+    switch (tl.variant) {
+        case GV_FULL: gram_consume<GV_FULL>(total, out, false, tl.diag != 0, ring, full, empty, rs); break;
+        case GV_HALF: gram_consume<GV_HALF>(total, out, false, tl.diag != 0, ring, full, empty, rs); break;
+        case GV_S8:   gram_consume<GV_S8>(total, out, false, tl.diag != 0, ring, full, empty, rs); break;
+        case GV_S4:   gram_consume<GV_S4>(total, out, false, tl.diag != 0, ring, full, empty, rs); break;
+        case GV_S3:   gram_consume<GV_S3>(total, out, false, tl.diag != 0, ring, full, empty, rs); break;
+        case GV_S2:   gram_consume<GV_S2>(total, out, false, tl.diag != 0, ring, full, empty, rs); break;
+        default:      gram_consume<GV_S1>(total, out, false, tl.diag != 0, ring, full, empty, rs); break;
+    }
+}
+
+// G tile = sum over the tile's parts (contiguous CTAs part_off[t] .. part_off[t+1]) and k-groups, fixed order
+__global__ void __launch_bounds__(256) k_gram_reduce_parts(const gram_tile* __restrict__ tiles, const int* __restrict__ part_off,
+                                                           const double* __restrict__ slots, double* __restrict__ G, int ldg,
+                                                           int* __restrict__ counters, int n_counters,
+                                                           const int* __restrict__ done) {
+    if (done && *done) return;
+    if (blockIdx.x == 0 && blockIdx.y == 0)
+        for (int i = threadIdx.x; i < n_counters; i += 256) counters[i] = 0;
+    const gram_tile tl = tiles[blockIdx.x];
+    const int TR = gv_rows(tl.variant), TC = gv_cols(tl.variant), KS = gv_ks(tl.variant);
+    const int p_lo = part_off[blockIdx.x], p_hi = part_off[blockIdx.x + 1];
+    for (int e = blockIdx.y * 256 + threadIdx.x; e < TR * TC; e += gridDim.y * 256) {
+        if (tl.diag && e / TC < 32 && e % TC >= 32) continue;
+        double sum = 0.0;
+        for (int q = p_lo; q < p_hi; ++q)
+            for (int k = 0; k < KS; ++k) sum += slots[(size_t)q * GR_SLOT + k * TR * TC + e];
+        const int r = tl.row0 + e / TC, c = tl.col0 + e % TC;
+        if (r < ldg && c < ldg) G[(int64_t)r * ldg + c] = sum;
+    }
+}
+
 // P clamped to >= minP (step-level entry point; inside dvf_fit_em the E-step stores P already clamped)
 __global__ void k_clamp_copy(const double* __restrict__ P, int64_t N, double minP, double* __restrict__ out) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x)
@@ -300,6 +390,10 @@ struct gram_host_plan {
     std::vector<gram_tile> tiles;
     std::vector<int> bundle_off, bundle_tiles;
     int n_groups = 1;
+    // parts schedule (used when it is predicted to be faster)
+    bool use_parts = false;
+    std::vector<gram_part> parts;
+    std::vector<int> part_off;
 };
 
 // a diagonal 64 x 64 tile runs 12 of its 16 warps
@@ -369,7 +463,37 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
             if (best_assign[i] == k) hp.bundle_tiles.push_back(i);
     }
     hp.bundle_off[best_g] = (int)hp.bundle_tiles.size();
+    // ---- parts schedule: p_t parts per tile, greedily lowering max(cost_t / p_t) until the SMs are used up ----
+    double parts_eff = 0.0;
+    if (nt <= n_sms && n_steps >= 4 * (int64_t)n_sms && g_parts != 0) {
+        std::vector<int> p(nt, 1);
+        for (int used = nt; used < n_sms; ++used) {
+            int arg = 0;
+            double worst = -1.0;
+            for (int i = 0; i < nt; ++i) {
+                const double c = tile_cost(hp.tiles[i]) / p[i];
+                if (c > worst) { worst = c; arg = i; }
+            }
+            p[arg]++;
+        }
+        double worst = 0.0;
+        int used = 0;
+        for (int i = 0; i < nt; ++i) { worst = std::max(worst, tile_cost(hp.tiles[i]) / p[i]); used += p[i]; }
+        parts_eff = total / (n_sms * worst);
+        // the bundle schedule reloads and stores its accumulators at every block: measured ~5 % on B200
+        if (g_parts > 0 || parts_eff > 0.95 * best_eff) {
+            hp.use_parts = true;
+            hp.part_off.assign(nt + 1, 0);
+            for (int i = 0; i < nt; ++i) {
+                hp.part_off[i] = (int)hp.parts.size();
+                for (int k = 0; k < p[i]; ++k) hp.parts.push_back(gram_part{i, k, p[i], 0});
+            }
+            hp.part_off[nt] = (int)hp.parts.size();
+            (void)used;
+        }
+    }
     if (g_debug) {
+        fprintf(stderr, "[gram plan] parts schedule: eff=%.3f %s\n", parts_eff, hp.use_parts ? "(used)" : "(not used)");
         int cnt[GV_COUNT] = {0};
         for (auto& tl : hp.tiles) cnt[tl.variant]++;
         fprintf(stderr, "[gram plan] N=%lld M=%d D=%d tiles=%d (full %d half %d s8 %d s4 %d s3 %d s2 %d s1 %d) bundles=%d groups=%d eff=%.3f\n",
@@ -389,13 +513,20 @@ gram_plan make_gram_plan(int64_t N, int D, int M) {
     pl.n_bundles = (int)hp.bundle_off.size() - 1;
     pl.n_groups = hp.n_groups;
     pl.n_ctas = pl.n_bundles * pl.n_groups;
+    pl.use_parts = hp.use_parts ? 1 : 0;
+    pl.n_parts = (int)hp.parts.size();
+    pl.sb_parts = g_sb_parts;
+    pl.n_counters = (int)(((N + GR_KC - 1) / GR_KC + g_sb_parts - 1) / g_sb_parts) + 1;
     size_t o = 0;
     pl.off_tiles = o;  o += al256(sizeof(gram_tile) * hp.tiles.size());
     pl.off_boff = o;   o += al256(sizeof(int) * hp.bundle_off.size());
     pl.off_btiles = o; o += al256(sizeof(int) * hp.bundle_tiles.size());
-    pl.off_progress = o; o += al256(sizeof(int) * (size_t)pl.n_ctas);
+    pl.off_progress = o; o += al256(sizeof(int) * (size_t)std::max(pl.n_ctas, pl.n_counters));
+    pl.off_parts = o;  o += al256(sizeof(gram_part) * hp.parts.size());
+    pl.off_poff = o;   o += al256(sizeof(int) * hp.part_off.size());
     pl.off_pclamp = o; o += al256(sizeof(double) * (size_t)(N + 2));
-    pl.off_slots = o;  o += sizeof(double) * (size_t)GR_SLOT * pl.n_tiles * pl.n_groups;
+    pl.off_slots = o;
+    o += sizeof(double) * (size_t)GR_SLOT * (pl.use_parts ? (size_t)pl.n_parts : (size_t)pl.n_tiles * pl.n_groups);
     pl.scratch_bytes = o;
     pl.sb = g_sb;
     pl.lag = g_lag;
@@ -411,7 +542,12 @@ int gram_prepare(const gram_plan& pl, int64_t N, int D, int M, void* scratch, cu
     DVF_CUDA(cudaMemcpyAsync(base + pl.off_tiles, hp.tiles.data(), sizeof(gram_tile) * hp.tiles.size(), cudaMemcpyHostToDevice, st));
     DVF_CUDA(cudaMemcpyAsync(base + pl.off_boff, hp.bundle_off.data(), sizeof(int) * hp.bundle_off.size(), cudaMemcpyHostToDevice, st));
     DVF_CUDA(cudaMemcpyAsync(base + pl.off_btiles, hp.bundle_tiles.data(), sizeof(int) * hp.bundle_tiles.size(), cudaMemcpyHostToDevice, st));
-    DVF_CUDA(cudaMemsetAsync(base + pl.off_progress, 0, sizeof(int) * (size_t)pl.n_ctas, st));
+    DVF_CUDA(cudaMemsetAsync(base + pl.off_progress, 0, sizeof(int) * (size_t)std::max(pl.n_ctas, pl.n_counters), st));
+    if (pl.use_parts) {
+        if ((int)hp.parts.size() != pl.n_parts) { set_error("gram plan changed between planning and preparation"); return DVF_ERR_ARG; }
+        DVF_CUDA(cudaMemcpyAsync(base + pl.off_parts, hp.parts.data(), sizeof(gram_part) * hp.parts.size(), cudaMemcpyHostToDevice, st));
+        DVF_CUDA(cudaMemcpyAsync(base + pl.off_poff, hp.part_off.data(), sizeof(int) * hp.part_off.size(), cudaMemcpyHostToDevice, st));
+    }
     return DVF_OK;
 }
 
@@ -422,6 +558,7 @@ int gram_run(const gram_plan& pl, const double* UY, const double* P, int64_t N, 
     static bool attr_set = false;
     if (!attr_set) {
         DVF_CUDA(cudaFuncSetAttribute(k_gram, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GR_SMEM));
+        DVF_CUDA(cudaFuncSetAttribute(k_gram_parts, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GR_SMEM));
         attr_set = true;
     }
     DVF_ARG(((uintptr_t)UY & 15) == 0 && ((uintptr_t)P & 15) == 0, "UY and P must be 16-byte aligned");
@@ -432,6 +569,15 @@ int gram_run(const gram_plan& pl, const double* UY, const double* P, int64_t N, 
     const gram_tile* tiles = (const gram_tile*)(base + pl.off_tiles);
     double* slots = (double*)(base + pl.off_slots);
     int* progress = (int*)(base + pl.off_progress);
+    if (pl.use_parts) {
+        k_gram_parts<<<pl.n_parts, GR_THREADS, GR_SMEM, st>>>(mapUY, mapP, N, tiles, (const gram_part*)(base + pl.off_parts),
+                                                            pl.sb_parts, pl.lag, slots, progress, done);
+        DVF_LAUNCH_CHECK();
+        k_gram_reduce_parts<<<dim3(pl.n_tiles, 4), 256, 0, st>>>(tiles, (const int*)(base + pl.off_poff), slots, G, pl.ldg,
+                                                                progress, pl.n_counters, done);
+        DVF_LAUNCH_CHECK();
+        return DVF_OK;
+    }
     k_gram<<<pl.n_ctas, GR_THREADS, GR_SMEM, st>>>(mapUY, mapP, N, tiles, pl.n_tiles, (const int*)(base + pl.off_boff),
                                                   (const int*)(base + pl.off_btiles), pl.n_bundles, pl.n_groups, pl.sb,
                                                   pl.lag, slots, progress, done);

@@ -12,7 +12,7 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $out/bench_r
 if [ -z "$NO_NCU" ]; then
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $out/launches_$tag.csv \
     python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline > $out/ncu_list_$tag.log 2>&1
-for k in k_gram k_jacobian_gemm k_dac k_update_v k_kernel_matrix; do
+for k in k_gram_parts k_gram k_jacobian_gemm k_dac k_update_v k_chol_solve; do
   timeout 600 ncu --set full --clock-control none --import-source on -k regex:"^$k\$" --launch-skip 1 -c 1 -f -o $out/${k}_$tag \
       python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline > $out/ncu_${k}_$tag.log 2>&1
 done
