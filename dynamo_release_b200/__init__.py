@@ -10,6 +10,14 @@ Drop-in names (same signatures as dynamo.vectorfield.scVectorField / dynamo.vect
 from .sparsevfc import SparseVFC, fit_em  # noqa: F401
 from .svc import SvcVectorField, vecfld_from_adata  # noqa: F401
 from .vf import (  # noqa: F401
+    Hessian_rkhs_gaussian,
+    Laplacian,
+    compute_curl,
+    compute_sensitivity,
+    compute_torsion,
+    elementwise_hessian_transformation,
+    hessian_transformation,
+    laplacian_rkhs,
     Jacobian_rkhs_gaussian,
     Jacobian_rkhs_gaussian_parallel,
     RkhsField,

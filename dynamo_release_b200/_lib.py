@@ -54,6 +54,8 @@ SIGNATURES = {
     "dvf_jacobian_det": (_i, [_p, _i64, _i, _p, _p]),
     "dvf_cell_angles": (_i, [_p, _p, _i64, _i, _p, _p]),
     "dvf_row_norms": (_i, [_p, _i64, _i, _p, _p]),
+    "dvf_hessian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
+    "dvf_laplacian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
     "dvf_fit_row_width": (_i64, [_i, _i]),
     "dvf_fit_workspace_bytes": (_i, [_i64, _i, _i, C.POINTER(_sz)]),
     "dvf_fit_em": (_i, [_p, _p, _i64, _i64, _i, _p, _i, _d, C.POINTER(EmParams), _p, _p, _p, _p, _p,

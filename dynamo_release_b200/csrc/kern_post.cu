@@ -147,6 +147,132 @@ k_row_norms(const double* __restrict__ V, int64_t n, int D, double* __restrict__
     if (lane == 0) out[c] = sqrt(s);
 }
 
+// ---- Hessian of the Gaussian-RKHS field (vectorfield/utils.py:589-614) -------------------------------------------
+//   H[i][l][m] = d^2 f_i / dx_l dx_m = -2 beta ( delta_lm v_i - 2 beta sum_j k_j C_ji d_jl d_jm ),  d_j = x - c_j
+// One CTA per cell.  Control points stream through shared memory in chunks of HS_JC (differences d_j and the rows
+// k_j C_j); a thread owns up to two (l <= m, block of 8 outputs i) units and keeps their 16 sums in registers; if
+// D (D+1) / 2 * ceil(D / 8) exceeds 1024 units the cell is done in several rounds.  Output: H[cell][i][l][m].
+constexpr int HS_JC = 32, HS_THREADS = 512, HS_IB = 8;
+
+__global__ void __launch_bounds__(HS_THREADS)
+k_hessian(const double* __restrict__ x, int64_t n, int D, const double* __restrict__ Xc, int M, double beta,
+          const double* __restrict__ C, double* __restrict__ H) {
+    extern __shared__ __align__(16) double hs_smem[];
+    const int DP = D + 1, DI = (D + HS_IB - 1) / HS_IB * HS_IB;
+    double* dj = hs_smem;                       // [HS_JC][DP]
+    double* kc = dj + HS_JC * DP;               // [HS_JC][DI]
+    double* xs = kc + HS_JC * DI;               // [D]
+    double* vs = xs + D;                        // [D]
+    double* kj = vs + D;                        // [HS_JC]
+    const int64_t cell = blockIdx.x;
+    const int tid = threadIdx.x;
+    for (int d = tid; d < D; d += HS_THREADS) { xs[d] = x[cell * D + d]; vs[d] = 0.0; }
+    const int n_pairs = D * (D + 1) / 2, n_ib = DI / HS_IB, n_units = n_pairs * n_ib;
+    double* Hc = H + cell * (int64_t)D * D * D;
+    for (int u0 = 0; u0 < n_units; u0 += 2 * HS_THREADS) {
+        int ul[2], um[2], ui[2];
+        bool live[2];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int u = u0 + tid + q * HS_THREADS;
+            live[q] = u < n_units;
+            int pr = live[q] ? u / n_ib : 0, l = 0;
+            ui[q] = live[q] ? (u % n_ib) * HS_IB : 0;
+            while (pr >= D - l) { pr -= D - l; ++l; }
+            ul[q] = l;
+            um[q] = l + pr;
+        }
+        double acc[2][HS_IB];
+#pragma unroll
+        for (int q = 0; q < 2; ++q)
+#pragma unroll
+            for (int i = 0; i < HS_IB; ++i) acc[q][i] = 0.0;
+        for (int j0 = 0; j0 < M; j0 += HS_JC) {
+            __syncthreads();
+            for (int e = tid; e < HS_JC * D; e += HS_THREADS) {
+                const int j = e / D, d = e - j * D;
+                dj[j * DP + d] = (j0 + j < M) ? xs[d] - Xc[(int64_t)(j0 + j) * D + d] : 0.0;
+            }
+            __syncthreads();
+            if (tid < HS_JC) {
+                double r2 = 0.0;
+                for (int d = 0; d < D; ++d) r2 = fma(dj[tid * DP + d], dj[tid * DP + d], r2);
+                kj[tid] = (j0 + tid < M) ? exp(-beta * r2) : 0.0;
+            }
+            __syncthreads();
+            for (int e = tid; e < HS_JC * DI; e += HS_THREADS) {
+                const int j = e / DI, i = e - j * DI;
+                kc[e] = (i < D && j0 + j < M) ? kj[j] * C[(int64_t)(j0 + j) * D + i] : 0.0;
+            }
+            __syncthreads();
+            if (u0 == 0 && tid < D) {          // v_i rides along in the first round
+                double v = vs[tid];
+                for (int j = 0; j < HS_JC; ++j) v += kc[j * DI + tid];
+                vs[tid] = v;
+            }
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                if (!live[q]) continue;
+                for (int j = 0; j < HS_JC; ++j) {
+                    const double pj = dj[j * DP + ul[q]] * dj[j * DP + um[q]];
+                    const double* kr = kc + j * DI + ui[q];
+#pragma unroll
+                    for (int i = 0; i < HS_IB; i += 2) {
+                        const double2 k2 = *reinterpret_cast<const double2*>(kr + i);
+                        acc[q][i] = fma(k2.x, pj, acc[q][i]);
+                        acc[q][i + 1] = fma(k2.y, pj, acc[q][i + 1]);
+                    }
+                }
+            }
+        }
+        __syncthreads();                        // vs complete (first round) before it is read below
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            if (!live[q]) continue;
+            const int l = ul[q], m = um[q];
+#pragma unroll
+            for (int i = 0; i < HS_IB; ++i) {
+                const int io = ui[q] + i;
+                if (io >= D) continue;
+                const double h = -2.0 * beta * ((l == m ? vs[io] : 0.0) - 2.0 * beta * acc[q][i]);
+                Hc[((int64_t)io * D + l) * D + m] = h;
+                Hc[((int64_t)io * D + m) * D + l] = h;
+            }
+        }
+    }
+}
+
+// ---- "Laplacian" as the reference computes it from its Hessian array (vectorfield/utils.py:665-687 applied to the
+// Hs[i, l, m, cell] of vector_calculus.py:413-417): L[k] = sum_a Hs[a, a, k] = sum_a d^2 f_a / dx_a dx_k
+//   = -2 beta sum_j k_j ( C_jk - 2 beta (C_j . d_j) d_jk ).   One warp per cell, lane = dimension (two if D > 32).
+__global__ void __launch_bounds__(256)
+k_laplacian(const double* __restrict__ x, int64_t n, int D, const double* __restrict__ Xc, int M, double beta,
+            const double* __restrict__ C, double* __restrict__ L) {
+    const int64_t cell = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (cell >= n) return;
+    const int d0 = lane, d1 = lane + 32;
+    const double x0 = d0 < D ? x[cell * D + d0] : 0.0, x1 = d1 < D ? x[cell * D + d1] : 0.0;
+    double a0 = 0.0, a1 = 0.0;
+    for (int j = 0; j < M; ++j) {
+        const double* c = Xc + (int64_t)j * D;
+        const double* cj = C + (int64_t)j * D;
+        const double e0 = d0 < D ? x0 - c[d0] : 0.0, e1 = d1 < D ? x1 - c[d1] : 0.0;
+        const double c0 = d0 < D ? cj[d0] : 0.0, c1 = d1 < D ? cj[d1] : 0.0;
+        double r2 = fma(e1, e1, e0 * e0), q = fma(c1, e1, c0 * e0);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            r2 += __shfl_xor_sync(0xffffffffu, r2, o);
+            q += __shfl_xor_sync(0xffffffffu, q, o);
+        }
+        const double k = exp(-beta * r2), w = 2.0 * beta * q;
+        a0 = fma(k, c0 - w * e0, a0);
+        a1 = fma(k, c1 - w * e1, a1);
+    }
+    if (d0 < D) L[cell * D + d0] = -2.0 * beta * a0;
+    if (d1 < D) L[cell * D + d1] = -2.0 * beta * a1;
+}
+
 }  // namespace dvf
 
 using namespace dvf;
@@ -190,6 +316,31 @@ extern "C" int dvf_row_norms(const double* V, int64_t n, int D, double* out, voi
     const int64_t blocks = (n + 7) / 8;
     DVF_ARG(blocks <= 0x7fffffff, "too many cells for one launch");
     k_row_norms<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(V, n, D, out);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}
+
+extern "C" int dvf_hessian(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                           double* H, void* stream) {
+    DVF_ARG(n >= 0 && D >= 1 && D <= kMaxD && M >= 1, "bad argument");
+    if (n == 0) return DVF_OK;
+    DVF_ARG(x && Xc && C && H, "null pointer");
+    DVF_ARG(n <= 0x7fffffff, "too many cells for one launch");
+    const int DP = D + 1, DI = (D + HS_IB - 1) / HS_IB * HS_IB;
+    const size_t smem = sizeof(double) * ((size_t)HS_JC * DP + (size_t)HS_JC * DI + 2 * D + HS_JC);
+    k_hessian<<<(unsigned)n, HS_THREADS, smem, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, H);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}
+
+extern "C" int dvf_laplacian(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                             double* L, void* stream) {
+    DVF_ARG(n >= 0 && D >= 1 && D <= kMaxD && M >= 1, "bad argument");
+    if (n == 0) return DVF_OK;
+    DVF_ARG(x && Xc && C && L, "null pointer");
+    const int64_t blocks = (n + 7) / 8;
+    DVF_ARG(blocks <= 0x7fffffff, "too many cells for one launch");
+    k_laplacian<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, L);
     DVF_LAUNCH_CHECK();
     return DVF_OK;
 }

@@ -144,6 +144,24 @@ def row_norms(V):
     return out
 
 
+def hessian(x, Xc, beta, Cm):
+    """K10 -- reference vectorfield/utils.py:589-614 for every row of x: (n, D, D, D), H[c, i, l, m]."""
+    x, Xc, Cm = _field(x, Xc, Cm)
+    n, D = x.shape
+    out = empty((n, D, D, D))
+    _lib.check(lib().dvf_hessian(ptr(x), n, D, ptr(Xc), Xc.shape[0], float(beta), ptr(Cm), ptr(out), stream_ptr()))
+    return out
+
+
+def laplacian(x, Xc, beta, Cm):
+    """K10 -- sum_a H[c, a, a, k] (reference utils.py:665-687 on the array of vector_calculus.py:413): (n, D)."""
+    x, Xc, Cm = _field(x, Xc, Cm)
+    n, D = x.shape
+    out = empty((n, D))
+    _lib.check(lib().dvf_laplacian(ptr(x), n, D, ptr(Xc), Xc.shape[0], float(beta), ptr(Cm), ptr(out), stream_ptr()))
+    return out
+
+
 def gene_transform(J, Qe, Qr, take_abs=False, group=None, n_groups=0, full=True):
     """K8 -- reference vectorfield/utils.py:544-554.  J (D, D, n) -> float32 (Ge, Gr, n) and/or group sums."""
     J, Qe, Qr = dev(J), dev(Qe), dev(Qr)

@@ -22,6 +22,13 @@ _NAMES = {
     "subset_jacobian_transformation": vf.subset_jacobian_transformation,
     "transform_jacobian": vf.transform_jacobian,
     "vector_transformation": vf.vector_transformation,
+    "Hessian_rkhs_gaussian": vf.Hessian_rkhs_gaussian,
+    "Laplacian": vf.Laplacian,
+    "hessian_transformation": vf.hessian_transformation,
+    "elementwise_hessian_transformation": vf.elementwise_hessian_transformation,
+    "compute_curl": vf.compute_curl,
+    "compute_torsion": vf.compute_torsion,
+    "compute_sensitivity": vf.compute_sensitivity,
     "vecfld_from_adata": svc.vecfld_from_adata,
     "SparseVFC": SparseVFC,
     "SvcVectorField": svc.SvcVectorField,

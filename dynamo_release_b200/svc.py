@@ -126,3 +126,36 @@ class SvcVectorField:
     def compute_curvature(self, X=None, method="analytical", formula=2, **kwargs):
         X = self.data["X"] if X is None else X
         return _vf.compute_curvature(self.func, self.get_Jacobian(method=method), X, formula=formula, **kwargs)
+
+    def compute_curl(self, X=None, method="analytical", dim1=0, dim2=1, dim3=2, **kwargs):
+        """reference scVectorField.py:806-838 (the reference slices X to the chosen 2 / 3 dimensions before it calls
+        the Jacobian, so like there this only works for 2- or 3-dimensional fields)."""
+        X = self.data["X"] if X is None else X
+        X = X[:, [dim1, dim2]] if (dim3 is None or X.shape[1] < 3) else X[:, [dim1, dim2, dim3]]
+        return _vf.compute_curl(self.get_Jacobian(method=method, **kwargs), X, **kwargs)
+
+    def compute_torsion(self, X=None, method="analytical", **kwargs):
+        """reference scVectorField.py:877-892."""
+        X = self.data["X"] if X is None else X
+        return _vf.compute_torsion(self.func, self.get_Jacobian(method=method), X, **kwargs)
+
+    def compute_sensitivity(self, X=None, method="analytical", **kwargs):
+        """reference scVectorField.py:894-909."""
+        X = self.data["X"] if X is None else X
+        return _vf.compute_sensitivity(self.get_Jacobian(method=method), X, **kwargs)
+
+    def get_Hessian(self, method="analytical", **kwargs):
+        """reference scVectorField.py:1090-1112."""
+        if method == "analytical":
+            return lambda x: _vf.Hessian_rkhs_gaussian(x, self.vf_dict, **kwargs)
+        if method == "numerical":
+            raise Exception("numerical Hessian for vector field is not defined.")
+        raise NotImplementedError(f"The method {method} is not implemented. Currently only supports 'analytical'.")
+
+    def get_Laplacian(self, method="analytical", **kwargs):
+        """reference scVectorField.py:1114-1135."""
+        if method == "analytical":
+            return lambda x: _vf.Laplacian(H=x)
+        if method == "numerical":
+            raise Exception("Numerical Laplacian for vector field is not defined.")
+        raise NotImplementedError(f"The method {method} is not implemented. Currently only supports 'analytical'.")

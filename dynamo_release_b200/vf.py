@@ -264,3 +264,100 @@ def cell_angles(U, V, device_out=False):
 def speed(V, device_out=False):
     """|v| per cell: reference vectorfield/vector_calculus.py:192."""
     return _out(kernels.row_norms(V), device_out)
+
+
+# ------------------------------------------------------------------------------------------------------
+# second derivatives and the low-dimensional calculus helpers (SURVEY 8f rank 2)
+# ------------------------------------------------------------------------------------------------------
+def Hessian_rkhs_gaussian(x, vf_dict, device_out=False):
+    """reference vectorfield/utils.py:589-614: H[i, l, m] = d^2 f_i / dx_l dx_m at the 1-D point x, (D, D, D).
+    Extension: a 2-D x (n, D) returns the (D, D, D, n) array dyn.vf.hessian assembles in its cell loop
+    (vector_calculus.py:413-417)."""
+    Xc, beta, C = _vf_parts(vf_dict)
+    x2, single = _as2d(x)
+    H = kernels.hessian(x2, Xc, beta, C)
+    H = H[0] if single else H.permute(1, 2, 3, 0).contiguous()
+    return _out(H, device_out)
+
+
+def Laplacian(H):
+    """reference vectorfield/utils.py:665-687: sum of the diagonal over the FIRST TWO axes of H, per remaining index;
+    (D, n) for the 4-D array of dyn.vf.hessian, (D, 1) for one cell's (D, D, D)."""
+    if torch.is_tensor(H):
+        L = torch.einsum("aak...->k...", H)
+        return L if H.dim() == 4 else L[:, None]
+    H = np.asarray(H)
+    L = np.einsum("aak...->k...", H)
+    return L if H.ndim == 4 else L[:, None]
+
+
+def laplacian_rkhs(x, vf_dict, device_out=False):
+    """Laplacian(Hessian(x)) of the reference for every row of x without forming any Hessian: (D, n) like
+    Laplacian() returns for the 4-D array ((D, 1) for a 1-D x)."""
+    Xc, beta, C = _vf_parts(vf_dict)
+    x2, single = _as2d(x)
+    return _out(kernels.laplacian(x2, Xc, beta, C).T.contiguous(), device_out)
+
+
+def hessian_transformation(H, qi, Qj, Qk):
+    """reference :617-640: h = Qj (sum_i q_i H_i..) Qk^T for one effector loading row qi."""
+    h = np.einsum("ijk, di -> djk", np.asarray(H), np.atleast_2d(qi))
+    return np.atleast_2d(Qj) @ h @ np.atleast_2d(Qk).T
+
+
+def elementwise_hessian_transformation(H, qi, qj, qk):
+    """reference :643-661: the scalar q_j^T (sum_i q_i H_i..) q_k."""
+    h = np.einsum("ijk, i -> jk", np.asarray(H), np.asarray(qi))
+    return np.asarray(qj) @ h @ np.asarray(qk)
+
+
+def _jac_on_device(f_jac, X):
+    """(D, D, n) CUDA tensor: fused path for our own Jacobian callables, any other callable is evaluated as given."""
+    if isinstance(f_jac, RkhsJacobian):
+        Xc, beta, C = _vf_parts(f_jac.vf_dict)
+        return kernels.jacobian(_as2d(X)[0], Xc, beta, C)
+    return dev(np.asarray(f_jac(X)))
+
+
+def compute_curl(f_jac, X, timeit=False, device_out=False):
+    """reference :887-905: 2-D: J[1,0] - J[0,1] per cell, (n,); 3-D: the curl vector per cell, stored as the
+    reference stores it -- broadcast over the rows of an (n, 3, 3) array."""
+    X = np.asarray(X) if not torch.is_tensor(X) else X
+    if X.shape[1] > 3:
+        raise Exception("curl is only defined in 2/3 dimension.")
+    J = _jac_on_device(f_jac, X)
+    if X.shape[1] == 2:
+        return _out(J[1, 0] - J[0, 1], device_out)
+    c = torch.stack([J[2, 1] - J[1, 2], J[0, 2] - J[2, 0], J[1, 0] - J[0, 1]], dim=1)     # (n, 3)
+    return _out(c[:, None, :].expand(-1, 3, -1).contiguous(), device_out)
+
+
+def compute_torsion(vf, f_jac, X, timeit=False, device_out=False):
+    """reference :823-841 with torsion_ (:760-766): tau = outer(v, a) (J a) / |outer(v, a)|_F^2 per cell (3-D only),
+    a 3-vector the reference broadcasts over the rows of an (n, 3, 3) array."""
+    X = np.asarray(X) if not torch.is_tensor(X) else X
+    if X.shape[1] != 3:
+        raise Exception("torsion is only defined in 3 dimension.")
+    J = _jac_on_device(f_jac, X)                                   # (3, 3, n)
+    if isinstance(vf, RkhsField):
+        Xc, beta, C = _vf_parts(vf.vf_dict)
+        v = kernels.eval_field(_as2d(X)[0], Xc, beta, C)
+    else:
+        v = dev(np.asarray(vf(X)))
+    a = torch.einsum("ijn,nj->ni", J, v)                            # acceleration_ : J v
+    Ja = torch.einsum("ijn,nj->ni", J, a)
+    va = v[:, :, None] * a[:, None, :]                              # outer(v, a)
+    tau = torch.einsum("nij,nj->ni", va, Ja) / (va * va).sum((1, 2))[:, None]
+    return _out(tau[:, None, :].expand(-1, 3, -1).contiguous(), device_out)
+
+
+def compute_sensitivity(f_jac, X, timeit=False, device_out=False):
+    """reference :844-870: S_c = (I - J_c)^-1 diag(1 / diag((I - J_c)^-1)), (D, D, n).  The batched inverse is the
+    library's (cuSOLVER through torch.linalg.inv); the Jacobians come from the fused kernel."""
+    X = np.asarray(X) if not torch.is_tensor(X) else X
+    J = _jac_on_device(f_jac, X)
+    D = J.shape[0]
+    A = torch.eye(D, dtype=torch.float64, device=J.device)[None] - J.permute(2, 0, 1)
+    s = torch.linalg.inv(A)
+    S = s / torch.diagonal(s, dim1=1, dim2=2)[:, None, :]
+    return _out(S.permute(1, 2, 0).contiguous(), device_out)

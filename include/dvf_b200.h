@@ -111,6 +111,16 @@ int dvf_jacobian_det(const double* J, int64_t n, int D, double* det, void* strea
 int dvf_cell_angles(const double* U, const double* V, int64_t n, int D, double* out, void* stream);
 int dvf_row_norms(const double* V, int64_t n, int D, double* out, void* stream);
 
+/* ---- K10: second derivatives of the field ----------------------------------------------------
+ * dvf_hessian: H[c][i][l][m] = d^2 f_i / dx_l dx_m at x_c  (n x D x D x D, cell-major).  replaces
+ *   Hessian_rkhs_gaussian, vectorfield/utils.py:589-614, and the per-cell loop of vector_calculus.py:413-417.
+ * dvf_laplacian: L[c][k] = sum_a H[c][a][a][k], what the reference's Laplacian() (utils.py:665-687) returns for the
+ *   Hs[i, l, m, cell] array of vector_calculus.py:413 -- computed directly from the field, no Hessian array. */
+int dvf_hessian(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                double* H, void* stream);
+int dvf_laplacian(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                  double* L, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * SparseVFC EM fit (vectorfield/scVectorField.py:417-497; Gaussian kernel branch)
  * ------------------------------------------------------------------------------------------- */

@@ -5,6 +5,9 @@ Run in the build container (needs /root/reference):   python -m oracle.gen_golde
 
   post_cells.npz : angle() per cell (vectorfield/utils.py:1148-1173, called at VectorField.py:255-259),
                    np.linalg.det per cell (vector_calculus.py:329), speed (vector_calculus.py:192)
+  post_hessian.npz: Hessian_rkhs_gaussian per cell (utils.py:589-614, loop of vector_calculus.py:413-417), Laplacian
+                   (utils.py:665-687), hessian_transformation / elementwise (:617-661), compute_curl (:887-905),
+                   compute_torsion (:823-841), compute_sensitivity (:844-870)
   rank_tables.npz: rank_jacobian_genes(..., return_df=True) (rank_vf.py:440-569) on a stand-in adata whose
                    uns['jacobian_pca']['jacobian_gene'] comes from the reference's own subset_jacobian_transformation
                    of the reference's own Jacobian_rkhs_gaussian; tables are stored as index arrays into the gene list
@@ -71,6 +74,35 @@ def main():
     out["det_cells"] = g["calc_cells"][:96]
     out["det"] = np.array([np.linalg.det(Js[:, :, i]) for i in np.arange(Js.shape[2])])
     np.savez_compressed(os.path.join(OUT, "post_cells.npz"), **out)
+
+    # ---- second derivatives, curl / torsion / sensitivity ----
+    h = {}
+    g12 = Golden("ragged_n1200_d12_m64")
+    vf12 = g12.vf()
+    xs12 = g12.X[g12["calc_cells"]][:6]
+    Hs = np.zeros([xs12.shape[1]] * 3 + [xs12.shape[0]])
+    for ind in range(xs12.shape[0]):
+        Hs[:, :, :, ind] = utils.Hessian_rkhs_gaussian(xs12[ind], vf12)          # vector_calculus.py:413-417
+    h["cells12"] = g12["calc_cells"][:6]
+    h["Hs12"] = Hs
+    h["L12"] = utils.Laplacian(Hs)
+    h["L12_single"] = utils.Laplacian(Hs[:, :, :, 0])
+    q = rng.standard_normal((4, xs12.shape[1]))
+    h["q"] = q
+    h["ht"] = utils.hessian_transformation(Hs[:, :, :, 1], q[:1], q[1:3], q[2:4])
+    h["het"] = utils.elementwise_hessian_transformation(Hs[:, :, :, 1], q[0], q[1], q[2])
+    f_jac12 = lambda x: utils.Jacobian_rkhs_gaussian(x, vf12)                    # noqa: E731
+    h["S12"] = utils.compute_sensitivity(f_jac12, xs12)
+    for D in (2, 3):
+        vfD = {"X_ctrl": rng.standard_normal((25, D)), "C": 0.3 * rng.standard_normal((25, D)), "beta": 0.4}
+        XD = rng.standard_normal((40, D))
+        f_jac = lambda x, vfD=vfD: utils.Jacobian_rkhs_gaussian(x, vfD)          # noqa: E731
+        f_vf = lambda x, vfD=vfD: utils.vector_field_function(x, vfD)            # noqa: E731
+        h["Xc_%d" % D], h["C_%d" % D], h["X_%d" % D] = vfD["X_ctrl"], vfD["C"], XD
+        h["curl_%d" % D] = utils.compute_curl(f_jac, XD)
+        if D == 3:
+            h["torsion_3"] = utils.compute_torsion(f_vf, f_jac, XD)
+    np.savez_compressed(os.path.join(OUT, "post_hessian.npz"), **h)
 
     # ---- ranking tables ----
     G = 14

@@ -305,6 +305,75 @@ def speed(V):
 
 
 # --------------------------------------------------------------------------------------------
+# second derivatives and low-dimensional calculus helpers
+# --------------------------------------------------------------------------------------------
+def hessian(x, vf):
+    """vectorfield/utils.py:589-614, one point x (1-D): H[i, l, m]."""
+    x = np.atleast_2d(x)
+    K, Dm = gauss_kernel(x, vf["X_ctrl"], vf["beta"], with_diff=True)     # K (1, M), Dm (1, D, M)
+    K = np.atleast_2d(K) * vf["C"].T                                      # (D, M): k_j C_ji
+    Dm = Dm.T                                                             # (M, D, 1)
+    Dm = np.eye(x.shape[1]) - 2 * vf["beta"] * Dm @ np.transpose(Dm, axes=(0, 2, 1))
+    return -2 * vf["beta"] * np.einsum("ij, jlm -> ilm", K, Dm)
+
+
+def hessian_cells(X, vf):
+    """vectorfield/vector_calculus.py:413-417: Hs[:, :, :, c] = Hessian(X[c])."""
+    Hs = np.zeros([X.shape[1], X.shape[1], X.shape[1], X.shape[0]])
+    for c in range(X.shape[0]):
+        Hs[:, :, :, c] = hessian(X[c], vf)
+    return Hs
+
+
+def laplacian_of(H):
+    """vectorfield/utils.py:665-687."""
+    if H.ndim == 4:
+        L = np.zeros([H.shape[2], H.shape[3]])
+        for c in range(H.shape[3]):
+            for k in range(L.shape[0]):
+                L[k, c] = np.diag(H[:, :, k, c]).sum()
+    else:
+        L = np.zeros([H.shape[2], 1])
+        for k in range(L.shape[0]):
+            L[k, 0] = np.diag(H[:, :, k]).sum()
+    return L
+
+
+def curl_cells(X, vf):
+    """vectorfield/utils.py:873-905 with the analytical Jacobian."""
+    n = len(X)
+    out = np.zeros(n) if X.shape[1] == 2 else np.zeros((n, 3, 3))
+    for i in range(n):
+        J = jacobian(X[i], vf)
+        out[i] = (J[1, 0] - J[0, 1]) if X.shape[1] == 2 else np.array([J[2, 1] - J[1, 2], J[0, 2] - J[2, 0], J[1, 0] - J[0, 1]])
+    return out
+
+
+def torsion_cells(X, vf):
+    """vectorfield/utils.py:760-766, 823-841."""
+    n = len(X)
+    tor = np.zeros((n, 3, 3))
+    v = field_eval(X, vf)
+    for i in range(n):
+        J = jacobian(X[i], vf)
+        a = J.dot(v[i][:, None]).flatten()
+        va = np.outer(v[i][:, None], a)
+        tor[i] = va.dot(J.dot(a)) / np.linalg.norm(va) ** 2
+    return tor
+
+
+def sensitivity_cells(X, vf):
+    """vectorfield/utils.py:844-870."""
+    J = jacobian(X, vf)
+    S = np.zeros_like(J)
+    eye = np.eye(J.shape[0])
+    for i in range(J.shape[2]):
+        s = np.linalg.inv(eye - J[:, :, i])
+        S[:, :, i] = s.dot(np.diag(1 / np.diag(s)))
+    return S
+
+
+# --------------------------------------------------------------------------------------------
 # normalisation (scVectorField.py:64-96, 138-182)
 # --------------------------------------------------------------------------------------------
 def normalise(X, V, fix_velocity=True):

@@ -377,6 +377,51 @@ def test_rank_tables_match_reference(pkg):
         assert rel(_np(Jm2[gi]), sw[:, :, lab2 == k].astype(np.float64).mean(2)) < 1e-6
 
 
+def test_second_derivatives_and_low_dim_calculus(pkg):
+    """K10: Hessian, the reference's Laplacian, curl, torsion, sensitivity against the vectors of
+    the executed reference (tests/golden/post/post_hessian.npz) and the oracle on other shapes."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "post", "post_hessian.npz"))
+    g = Golden("ragged_n1200_d12_m64")
+    vf, xs = g.vf(), g.X[z["cells12"]]
+    Hs = pkg.Hessian_rkhs_gaussian(xs, vf)                       # (D, D, D, n) extension
+    assert Hs.shape == z["Hs12"].shape and rel(Hs, z["Hs12"]) < 1e-11
+    H1 = pkg.Hessian_rkhs_gaussian(xs[1], vf)                    # the reference's 1-D call
+    assert H1.shape == (12, 12, 12) and rel(H1, z["Hs12"][:, :, :, 1]) < 1e-11
+    assert np.array_equal(H1, np.transpose(H1, (0, 2, 1)))       # symmetric in the two derivative indices
+    assert rel(pkg.Laplacian(Hs), z["L12"]) < 1e-11 and rel(pkg.Laplacian(Hs[:, :, :, 0]), z["L12_single"]) < 1e-11
+    assert rel(pkg.laplacian_rkhs(xs, vf), z["L12"]) < 1e-11     # fused: no Hessian array
+    q = z["q"]
+    assert rel(pkg.hessian_transformation(H1, q[:1], q[1:3], q[2:4]), z["ht"]) < 1e-11
+    assert rel(pkg.elementwise_hessian_transformation(H1, q[0], q[1], q[2]), z["het"]) < 1e-11
+    f_jac = pkg.RkhsJacobian(vf)
+    assert rel(pkg.compute_sensitivity(f_jac, xs), z["S12"]) < 1e-9
+    for D in (2, 3):
+        vfd = {"X_ctrl": z["Xc_%d" % D], "C": z["C_%d" % D], "beta": 0.4}
+        got = pkg.compute_curl(pkg.RkhsJacobian(vfd), z["X_%d" % D])
+        assert got.shape == z["curl_%d" % D].shape and rel(got, z["curl_%d" % D]) < 1e-12
+    vf3 = {"X_ctrl": z["Xc_3"], "C": z["C_3"], "beta": 0.4}
+    tor = pkg.compute_torsion(pkg.RkhsField(vf3), pkg.RkhsJacobian(vf3), z["X_3"])
+    assert tor.shape == z["torsion_3"].shape and rel(tor, z["torsion_3"]) < 1e-11
+    # generic callables (not ours) go through the same post-processing
+    assert rel(pkg.compute_curl(lambda x: o.jacobian(x, vf3), z["X_3"]), z["curl_3"]) < 1e-12
+    with pytest.raises(Exception):
+        pkg.compute_curl(f_jac, xs)                              # 12-D: "curl is only defined in 2/3 dimension."
+    # larger dimensions: several unit rounds in the Hessian kernel (D = 50), two values per lane in the Laplacian
+    for name in ("hema_n1500_d50_m160", "hema_n2000_d30_m100"):
+        g2 = Golden(name)
+        vf2, x2 = g2.vf(), g2.X[g2["calc_cells"]][:5]
+        H2 = pkg.Hessian_rkhs_gaussian(x2, vf2)
+        ref = o.hessian_cells(x2, vf2)
+        assert rel(H2, ref) < 1e-11
+        assert rel(pkg.laplacian_rkhs(x2, vf2), o.laplacian_of(ref)) < 1e-11
+    # class methods
+    vfc = pkg.SvcVectorField()
+    vfc.vf_dict = vf
+    assert rel(vfc.get_Hessian()(xs[2]), z["Hs12"][:, :, :, 2]) < 1e-11
+    assert rel(vfc.get_Laplacian()(z["Hs12"]), z["L12"]) < 1e-13
+
+
 def test_edge_cases(pkg):
     rng = np.random.default_rng(1)
     vf = {"X_ctrl": rng.normal(size=(7, 3)), "beta": 0.3, "C": rng.normal(size=(7, 3))}

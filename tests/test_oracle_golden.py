@@ -68,3 +68,20 @@ def test_oracle_postprocessing_matches_reference():
     # the Jacobians agree to 1e-13; a determinant moves by n * eps * cond relative to that
     cond = np.array([np.linalg.cond(Js[:, :, i]) for i in range(Js.shape[2])])
     assert np.all(np.abs(o.jacobian_det(Js) - z["det"]) <= 1e-12 * cond * np.abs(z["det"]))
+
+
+def test_oracle_second_derivatives_match_reference():
+    """Hessian / Laplacian / curl / torsion / sensitivity restatements against the executed reference."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "post", "post_hessian.npz"))
+    g = Golden("ragged_n1200_d12_m64")
+    vf, xs = g.vf(), g.X[z["cells12"]]
+    Hs = o.hessian_cells(xs, vf)
+    assert rel(Hs, z["Hs12"]) < 1e-13
+    assert rel(o.laplacian_of(Hs), z["L12"]) < 1e-13 and rel(o.laplacian_of(Hs[:, :, :, 0]), z["L12_single"]) < 1e-13
+    assert rel(o.sensitivity_cells(xs, vf), z["S12"]) < 1e-10
+    for D in (2, 3):
+        vfd = {"X_ctrl": z["Xc_%d" % D], "C": z["C_%d" % D], "beta": 0.4}
+        assert rel(o.curl_cells(z["X_%d" % D], vfd), z["curl_%d" % D]) < 1e-13
+    vf3 = {"X_ctrl": z["Xc_3"], "C": z["C_3"], "beta": 0.4}
+    assert rel(o.torsion_cells(z["X_3"], vf3), z["torsion_3"]) < 1e-12
