@@ -115,6 +115,65 @@ def div_acc_curv(x, Xc, beta, Cm, formula=2, want=("v", "div", "acc", "acc_norm"
     return out
 
 
+DAC_STREAM_CHUNK = 131072     # cells per pipelined slab of the host-to-host path below
+
+
+def _in_stream():
+    d = ("in", torch.cuda.current_device())
+    if d not in _SIDE:
+        _SIDE[d] = torch.cuda.Stream(device=d[1])
+    return _SIDE[d]
+
+
+def div_acc_curv_host(X, Xc, beta, Cm, formula=2, want=("acc", "acc_norm")):
+    """K7 for a host array X with the requested outputs delivered as NumPy arrays: cell slabs go host -> device on one
+    stream, through the fused kernel on the compute stream and device -> pinned host on a third, two slabs in flight,
+    so for n >> slab the call costs about max(H2D, kernel, D2H) instead of their sum."""
+    Xh = np.ascontiguousarray(np.asarray(X), dtype=np.float64)
+    n, D = Xh.shape
+    Xc, Cm = dev(Xc), dev(Cm)
+    if formula == 1:
+        want = tuple(k for k in want if k != "curv")
+    shapes = {"v": (n, D), "div": (n,), "acc": (n, D), "acc_norm": (n,), "curv": (n, D), "curv_norm": (n,)}
+    res = {k: torch.empty(shapes[k], dtype=torch.float64, pin_memory=True) for k in want}
+    if n == 0:
+        return {k: v.numpy() for k, v in res.items()}
+    ch = min(DAC_STREAM_CHUNK, n)
+    nbuf = 2 if n > ch else 1
+    xin = [torch.empty((ch, D), dtype=torch.float64, device="cuda") for _ in range(nbuf)]
+    dout = [{k: torch.empty((ch,) + shapes[k][1:], dtype=torch.float64, device="cuda") for k in want} for _ in range(nbuf)]
+    main, s_in, s_out = torch.cuda.current_stream(), _in_stream(), _side_stream()
+    Xt = torch.from_numpy(Xh)
+    computed, drained = [None] * nbuf, [None] * nbuf
+    L = lib()
+    for k, c0 in enumerate(range(0, n, ch)):
+        nc = min(ch, n - c0)
+        b = k % nbuf
+        if computed[b] is not None:
+            s_in.wait_event(computed[b])          # the input slab buffer has been consumed
+        with torch.cuda.stream(s_in):
+            xin[b][:nc].copy_(Xt[c0:c0 + nc], non_blocking=True)
+        loaded = torch.cuda.Event()
+        loaded.record(s_in)
+        main.wait_event(loaded)
+        if drained[b] is not None:
+            main.wait_event(drained[b])           # the output slab buffers have been copied out
+        o = dout[b]
+        _lib.check(L.dvf_div_acc_curv(xin[b].data_ptr(), nc, D, ptr(Xc), Xc.shape[0], float(beta), ptr(Cm), int(formula),
+                                      ptr(o.get("v")), ptr(o.get("div")), ptr(o.get("acc")), ptr(o.get("acc_norm")),
+                                      ptr(o.get("curv")), ptr(o.get("curv_norm")), main.cuda_stream))
+        computed[b] = torch.cuda.Event()
+        computed[b].record(main)
+        s_out.wait_event(computed[b])
+        with torch.cuda.stream(s_out):
+            for key in want:
+                res[key][c0:c0 + nc].copy_(o[key][:nc], non_blocking=True)
+        drained[b] = torch.cuda.Event()
+        drained[b].record(s_out)
+    s_out.synchronize()
+    return {k: v.numpy() for k, v in res.items()}
+
+
 def jacobian_det(J):
     """K9 -- reference vector_calculus.py:329: det of every cell's Jacobian, J (D, D, n) -> (n,)."""
     J = dev(J)

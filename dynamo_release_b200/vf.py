@@ -127,6 +127,11 @@ class RkhsField:
         return vector_field_function(x, self.vf_dict, **kw)
 
 
+def _host_pipeline(X, device_out):
+    """numpy in -> numpy out with enough cells to overlap the copies with the kernel (kernels.div_acc_curv_host)."""
+    return (not device_out) and (not torch.is_tensor(X)) and np.ndim(X) == 2 and np.shape(X)[0] >= 2 * kernels.DAC_STREAM_CHUNK
+
+
 def _generic_vJ(vf, f_jac, X, Js):
     """Generic callables (reference semantics): evaluate them, continue on the device."""
     v = dev(vf(X)) if vf is not None else None
@@ -139,6 +144,8 @@ def compute_divergence(f_jac, X, Js=None, vectorize_size=1000, timeit=False, dev
     d = _fused_ok(None, f_jac, Js)
     if d is not None:
         Xc, beta, C = _vf_parts(d)
+        if _host_pipeline(X, device_out):
+            return kernels.div_acc_curv_host(X, Xc, beta, C, want=("div",))["div"]
         return _out(kernels.div_acc_curv(X, Xc, beta, C, want=("div",))["div"], device_out)
     _, J = _generic_vJ(None, f_jac, X, Js)
     return _out(torch.einsum("iin->n", J), device_out)
@@ -149,6 +156,9 @@ def compute_acceleration(vf, f_jac, X, Js=None, return_all=False, timeit=False, 
     d = _fused_ok(vf, f_jac, Js)
     if d is not None:
         Xc, beta, C = _vf_parts(d)
+        if not return_all and _host_pipeline(X, device_out):
+            r = kernels.div_acc_curv_host(X, Xc, beta, C, want=("acc", "acc_norm"))
+            return r["acc_norm"], r["acc"]
         r = kernels.div_acc_curv(X, Xc, beta, C, want=("v", "acc", "acc_norm") if return_all else ("acc", "acc_norm"))
         if return_all:
             J = kernels.jacobian(X, Xc, beta, C)
@@ -169,6 +179,9 @@ def compute_curvature(vf, f_jac, X, Js=None, formula=2, timeit=False, device_out
     if d is not None:
         Xc, beta, C = _vf_parts(d)
         want = ("curv", "curv_norm") if formula == 2 else ("curv_norm",)
+        if _host_pipeline(X, device_out):
+            r = kernels.div_acc_curv_host(X, Xc, beta, C, formula=formula, want=want)
+            return r["curv_norm"], r.get("curv")
         r = kernels.div_acc_curv(X, Xc, beta, C, formula=formula, want=want)
         return _out(r["curv_norm"], device_out), (None if formula != 2 else _out(r["curv"], device_out))
     v, J = _generic_vJ(vf, f_jac, X, Js)

@@ -422,6 +422,50 @@ def test_second_derivatives_and_low_dim_calculus(pkg):
     assert rel(vfc.get_Laplacian()(z["Hs12"]), z["L12"]) < 1e-13
 
 
+def test_gram_schedules_against_fp64_matmul():
+    """The weighted Gram + RHS kernel under both schedules (parts: few tiles; bundles: many tiles or few cells) and
+    every tile shape, against an FP64 matmul of the same operands (lower triangle, 8-column granularity), and its
+    bitwise reproducibility run to run.  Size-independent property: the result only depends on the operands."""
+    from dynamo_release_b200 import kernels as k
+    torch.manual_seed(7)
+    for N, M, D in ((60001, 500, 30), (40000, 1000, 50), (3000, 100, 2), (150000, 100, 30), (33000, 333, 17),
+                    (70000, 200, 50), (100, 20, 3), (25000, 64, 12)):
+        W = k.row_width(M, D)
+        UY = torch.rand((N, W), dtype=torch.float64, device="cuda")
+        UY[:, M + D:] = 0
+        P = torch.rand((N,), dtype=torch.float64, device="cuda")
+        G = k.gram(UY, P, 1e-5, D, M)
+        ref = (UY * P.clamp_min(1e-5)[:, None]).T @ UY
+        K = M + D
+        tri = torch.tril(torch.ones((K, K), dtype=torch.bool, device="cuda"))
+        err = float(((G[:K, :K] - ref[:K, :K]).abs() * tri).max() / ref.abs().max())
+        assert err < 2e-14, (N, M, D, err)
+        for _ in range(3):
+            assert torch.equal(k.gram(UY, P, 1e-5, D, M)[:K, :K] * tri, G[:K, :K] * tri), (N, M, D)
+
+
+def test_host_pipeline_equals_single_launch(pkg):
+    """numpy-in / numpy-out divergence, acceleration, curvature stream their cells through the kernel in slabs
+    (kernels.div_acc_curv_host); the slabs must reproduce the single launch bit for bit, ragged tail included."""
+    from dynamo_release_b200 import kernels as k
+    g = Golden("ragged_n1200_d12_m64")
+    vf = g.vf()
+    rng = np.random.default_rng(11)
+    n = 2 * k.DAC_STREAM_CHUNK + 777
+    X = g.X[rng.integers(0, len(g.X), n)] + 0.01 * rng.standard_normal((n, g.X.shape[1]))
+    f_jac, func = pkg.RkhsJacobian(vf), pkg.RkhsField(vf)
+    Xd = torch.from_numpy(X).cuda()
+    assert np.array_equal(pkg.compute_divergence(f_jac, X), _np(pkg.compute_divergence(f_jac, Xd, device_out=True)))
+    a, am = pkg.compute_acceleration(func, f_jac, X)
+    a2, am2 = pkg.compute_acceleration(func, f_jac, Xd, device_out=True)
+    assert np.array_equal(a, _np(a2)) and np.array_equal(am, _np(am2))
+    for formula in (1, 2):
+        c, cm = pkg.compute_curvature(func, f_jac, X, formula=formula)
+        c2, cm2 = pkg.compute_curvature(func, f_jac, Xd, formula=formula, device_out=True)
+        assert np.array_equal(c, _np(c2))
+        assert (cm is None and cm2 is None) or np.array_equal(cm, _np(cm2))
+
+
 def test_edge_cases(pkg):
     rng = np.random.default_rng(1)
     vf = {"X_ctrl": rng.normal(size=(7, 3)), "beta": 0.3, "C": rng.normal(size=(7, 3))}
