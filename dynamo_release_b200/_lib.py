@@ -73,6 +73,9 @@ SIGNATURES = {
     "dvf_comm_allreduce_sum": (_i, [_p, _p, _i64, _p]),
     "dvf_host_cdf": (_i, [_p, _i64, _p]),
     "dvf_host_scale": (_i, [_p, _i64, C.c_double, _p]),
+    "dvf_host_pairwise_sum": (_i, [_p, _i64, _p]),
+    "dvf_host_choice_cumsum": (_i, [_p, _i64, C.c_double, _p, _i64, _p]),
+    "dvf_host_searchsorted_div": (_i, [_p, _i64, _p, _i64, _p]),
     "dvf_memcpy2d_async": (_i, [_p, _sz, _p, _sz, _sz, _sz, _i, _p]),
 }
 

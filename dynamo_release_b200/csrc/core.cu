@@ -167,6 +167,75 @@ extern "C" int dvf_host_cdf(const double* p, int64_t n, double* cdf) {
     return DVF_OK;
 }
 
+// ---- numpy.sum of a contiguous float64 vector, bit for bit: NumPy's pairwise summation (8 interleaved partial sums
+// on blocks of <= 128 elements, halves split at a multiple of 8 above that), with the top levels of the recursion
+// spread over threads -- the tree, and therefore every rounding, is the same as in the serial recursion.
+static double pw_sum(const double* a, int64_t n) {
+    if (n < 8) {
+        double res = 0.0;
+        for (int64_t i = 0; i < n; ++i) res += a[i];
+        return res;
+    }
+    if (n <= 128) {
+        double r[8];
+        for (int j = 0; j < 8; ++j) r[j] = a[j];
+        int64_t i = 8;
+        for (; i < n - (n % 8); i += 8)
+            for (int j = 0; j < 8; ++j) r[j] += a[i + j];
+        double res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+        for (; i < n; ++i) res += a[i];
+        return res;
+    }
+    int64_t n2 = n / 2;
+    n2 -= n2 % 8;
+    return pw_sum(a, n2) + pw_sum(a + n2, n - n2);
+}
+static double pw_sum_par(const double* a, int64_t n, int depth) {
+    if (depth <= 0 || n <= (1 << 16)) return pw_sum(a, n);
+    int64_t n2 = n / 2;
+    n2 -= n2 % 8;
+    double left = 0.0;
+    std::thread th([&] { left = pw_sum_par(a, n2, depth - 1); });
+    const double right = pw_sum_par(a + n2, n - n2, depth - 1);
+    th.join();
+    return left + right;
+}
+extern "C" int dvf_host_pairwise_sum(const double* a, int64_t n, double* out) {
+    DVF_ARG(out && (a || n == 0) && n >= 0, "bad argument");
+    *out = 0.0 + pw_sum_par(a, n, 3);
+    return DVF_OK;
+}
+
+// raw[i] = sum_{k <= i} p_k, p_k = v[k] / total except p_k = 0 for the (ascending) indices in `skip`: the strictly
+// sequential cumulative sum of Generator.choice's p (numpy/random/_generator.pyx, replace=False), formed in place.
+extern "C" int dvf_host_choice_cumsum(const double* v, int64_t n, double total, const int64_t* skip, int64_t n_skip,
+                                      double* raw) {
+    DVF_ARG(v && raw && n >= 1 && (skip || n_skip == 0), "bad argument");
+    // the quotients are independent (threads); only the additions have to run one after the other
+    host_parallel_for(n, [=](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) raw[i] = v[i] / total; });
+    for (int64_t s = 0; s < n_skip; ++s)
+        if (skip[s] >= 0 && skip[s] < n) raw[skip[s]] = 0.0;
+    double acc = 0.0;
+    for (int64_t i = 0; i < n; ++i) { acc += raw[i]; raw[i] = acc; }
+    return DVF_OK;
+}
+
+// out[q] = numpy.searchsorted(raw / raw[n-1], x[q], side='right') without forming the quotient array: the first i
+// with raw[i] / last > x (division by a positive constant keeps the order, so bisection on the fly is exact)
+extern "C" int dvf_host_searchsorted_div(const double* raw, int64_t n, const double* x, int64_t m, int64_t* out) {
+    DVF_ARG(raw && x && out && n >= 1 && m >= 0, "bad argument");
+    const double last = raw[n - 1];
+    for (int64_t q = 0; q < m; ++q) {
+        int64_t lo = 0, hi = n;
+        while (lo < hi) {
+            const int64_t mid = lo + (hi - lo) / 2;
+            if (raw[mid] / last > x[q]) hi = mid; else lo = mid + 1;
+        }
+        out[q] = lo;
+    }
+    return DVF_OK;
+}
+
 extern "C" int dvf_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width_bytes,
                                   size_t height, int to_host, void* stream) {
     DVF_ARG(dst && src && dpitch >= width_bytes && spitch >= width_bytes, "bad argument");

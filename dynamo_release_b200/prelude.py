@@ -122,31 +122,55 @@ def row_norms(Y: torch.Tensor) -> torch.Tensor:
     return torch.sqrt(ss) if ss.is_cuda else torch.from_numpy(np.sqrt(ss.numpy()))
 
 
+_HOST_BUF = {}
+
+
+def _host_buffer(name: str, n: int) -> np.ndarray:
+    """Reusable host scratch (fresh 64 MB arrays cost more in page faults than the pass that fills them)."""
+    buf = _HOST_BUF.get(name)
+    if buf is None or buf.shape[0] < n:
+        buf = _HOST_BUF[name] = np.empty(max(n, 1 << 16), dtype=np.float64)
+    return buf[:n]
+
+
+def numpy_sum(a: np.ndarray) -> float:
+    """np.sum of a contiguous float64 vector, bit for bit (NumPy's pairwise tree), on a few threads."""
+    from . import _lib
+    import ctypes as C
+    out = C.c_double(0.0)
+    _lib.check(_lib.load().dvf_host_pairwise_sum(a.ctypes.data_as(C.c_void_p), a.shape[0], C.byref(out)))
+    return out.value
+
+
 def velocity_weighted_choice(speed: np.ndarray, M: int, seed: int) -> np.ndarray:
     """tools/sampling.py:242-245: default_rng(seed).choice(arange(n), size=M, p=speed/sum(speed), replace=False).
 
     The random stream is numpy's own (Generator.random); the rest restates Generator.choice's replace=False
     algorithm (numpy/random/_generator.pyx: draw uniforms, cdf = cumsum(p) / cdf[-1], searchsorted(side='right'),
-    keep first occurrences, zero the found entries and repeat) with the O(n) passes fused into one C helper
-    (dvf_host_cdf: the same strictly sequential double-precision accumulation as numpy.cumsum), so the chosen
-    cells are identical -- tests/test_prelude_cpu.py checks it against Generator.choice itself."""
+    keep first occurrences, zero the found entries and repeat) with its O(n) passes reduced to what the result
+    needs, each bit-identical to NumPy's: total = np.sum(speed) by the same pairwise tree (dvf_host_pairwise_sum),
+    the strictly sequential cumulative sum of speed / total with the found cells skipped (dvf_host_choice_cumsum;
+    p itself is never stored), and the bisection evaluated on raw[i] / raw[-1] on the fly
+    (dvf_host_searchsorted_div; the normalised array is never formed).  The chosen cells are identical --
+    tests/test_prelude_cpu.py checks them against Generator.choice itself."""
     from . import _lib
     import ctypes as C
     speed = np.ascontiguousarray(speed, dtype=np.float64)
     n = speed.shape[0]
     rng = np.random.default_rng(seed)
     lib = _lib.load()
-    p = np.empty(n, dtype=np.float64)
-    _lib.check(lib.dvf_host_scale(speed.ctypes.data_as(C.c_void_p), n, float(np.sum(speed)), p.ctypes.data_as(C.c_void_p)))
-    cdf = np.empty(n, dtype=np.float64)
+    total = numpy_sum(speed)
+    raw = _host_buffer("raw", n)
     found = np.zeros(M, dtype=np.int64)
     n_uniq = 0
     while n_uniq < M:
         x = rng.random((M - n_uniq,))
-        if n_uniq > 0:
-            p[found[0:n_uniq]] = 0
-        _lib.check(lib.dvf_host_cdf(p.ctypes.data_as(C.c_void_p), n, cdf.ctypes.data_as(C.c_void_p)))
-        new = cdf.searchsorted(x, side="right")
+        skip = np.sort(found[0:n_uniq])
+        _lib.check(lib.dvf_host_choice_cumsum(speed.ctypes.data_as(C.c_void_p), n, total, skip.ctypes.data_as(C.c_void_p),
+                                              n_uniq, raw.ctypes.data_as(C.c_void_p)))
+        new = np.empty(x.shape[0], dtype=np.int64)
+        _lib.check(lib.dvf_host_searchsorted_div(raw.ctypes.data_as(C.c_void_p), n, x.ctypes.data_as(C.c_void_p), x.shape[0],
+                                                 new.ctypes.data_as(C.c_void_p)))
         _, unique_indices = np.unique(new, return_index=True)
         unique_indices.sort()
         new = new.take(unique_indices)
