@@ -103,24 +103,48 @@ def sharded_prelude(Xv, Yv, M, seed=0, beta=None, velocity_based_sampling=True):
     Returns (ctrl_t, idx (numpy), beta, n_total) on every rank."""
     rank = dist.get_rank()
     D = Xv.shape[1]
+    import os
+    import sys
+    import time
+    timing = os.environ.get("DVF_PRELUDE_TIMING") and rank == 0   # developer aid: phase times on rank 0
+    marks = []
+
+    def mark(name):
+        if timing:
+            if Xv.is_cuda:
+                torch.cuda.synchronize()
+            marks.append((name, time.perf_counter()))
+
+    mark("start")
     key, counts = gather_rows(Xv[:, 0].contiguous())
     speed = gather_rows(prelude.row_norms(Yv))[0] if velocity_based_sampling else None
+    mark("gather keys+speeds")
     n_total = int(sum(counts))
     srv = RowServer(Xv, counts)
     meta = torch.zeros(2, dtype=torch.float64, device=Xv.device)
     if rank == 0:
         first = prelude.unique_first(key, srv.fetch)
+        mark("sort + ties")
         n_u = first.numel()
         m_eff = min(int(M), n_u)
         if velocity_based_sampling:
-            idx = prelude.velocity_weighted_choice(prelude.host_f64(speed[first]), m_eff, seed)
+            sp = prelude.host_f64(speed[first])
+            mark("speeds to host")
+            idx = prelude.velocity_weighted_choice(sp, m_eff, seed)
+            mark("host choice")
         else:
             idx = np.random.RandomState(seed=seed).permutation(n_u)[:m_eff]  # scVectorField.py:409-410
         idx_t = torch.as_tensor(idx, dtype=torch.int64, device=Xv.device)
         ctrl_t = srv.fetch(first[idx_t])
+        mark("fetch ctrl rows")
         if beta is None:
             beta = 1.0 / prelude.bandwidth(ctrl_t) ** 2
+        mark("bandwidth")
         meta[0], meta[1] = float(m_eff), float(beta)
+        if timing:
+            print("[sharded prelude] n=%d: " % n_total + ", ".join("%s %.1f ms" % (b[0], (b[1] - a[1]) * 1e3)
+                                                                    for a, b in zip(marks[:-1], marks[1:])),
+                  file=sys.stderr, flush=True)
     else:
         srv.fetch()
         srv.fetch()

@@ -466,6 +466,38 @@ def test_host_pipeline_equals_single_launch(pkg):
         assert (cm is None and cm2 is None) or np.array_equal(cm, _np(cm2))
 
 
+def test_solver_and_update_large_M():
+    """The control-point solve and V = U C at control-point counts beyond the golden cases (M up to 2000, ragged
+    panel sizes), against NumPy on the same well-conditioned system."""
+    from dynamo_release_b200 import kernels as k
+    rng = np.random.default_rng(2)
+    for M, D in ((1500, 30), (2000, 50), (1025, 7), (333, 64)):
+        W = k.row_width(M, D)
+        A = rng.standard_normal((M + 200, M)) / np.sqrt(M)
+        lhs0 = A.T @ A                                           # PSD Gram part
+        Kc = np.exp(-0.5 * np.abs(np.subtract.outer(np.arange(M), np.arange(M))) / M) + np.eye(M)
+        rhs = rng.standard_normal((M, D))
+        G = np.zeros((W, W))
+        G[:M, :M] = np.tril(lhs0)                                # only the lower triangle is ever read
+        G[M:M + D, :M] = rhs.T
+        lam = 0.37
+        C_gpu, info = k.solve(G, Kc, M, D, lam)
+        assert info == 0
+        C_ref = np.linalg.solve(lhs0 + lam * Kc, rhs)
+        assert rel(_np(C_gpu), C_ref) < 1e-11, (M, D)
+        # V = U C, r2, sum P r2 on a few thousand cells
+        N = 3000
+        UY = np.zeros((N, W))
+        UY[:, :M] = rng.random((N, M))
+        UY[:, M:M + D] = rng.standard_normal((N, D))
+        P = rng.random(N)
+        V, r2, s = k.update_v(UY, C_ref, P, 1e-5, D, M)
+        Vr = UY[:, :M] @ C_ref
+        assert rel(_np(V), Vr) < 1e-13
+        r2r = np.sum((UY[:, M:M + D] - Vr) ** 2, 1)
+        assert rel(_np(r2), r2r) < 1e-12 and abs(float(s) - np.sum(np.maximum(P, 1e-5) * r2r)) <= 1e-11 * np.sum(r2r)
+
+
 def test_edge_cases(pkg):
     rng = np.random.default_rng(1)
     vf = {"X_ctrl": rng.normal(size=(7, 3)), "beta": 0.3, "C": rng.normal(size=(7, 3))}
