@@ -498,6 +498,60 @@ def test_solver_and_update_large_M():
         assert rel(_np(r2), r2r) < 1e-12 and abs(float(s) - np.sum(np.maximum(P, 1e-5) * r2r)) <= 1e-11 * np.sum(r2r)
 
 
+def test_random_shapes_against_oracle(pkg):
+    """Seeded sweep over ragged shapes (n, D, M from 1 upward, odd counts, D up to the 64 the kernels support): every
+    evaluation entry point against the NumPy oracle.  Catches tile-boundary and padding mistakes the golden cases
+    (D in {2, 12, 30, 50}) cannot."""
+    from dynamo_release_b200 import kernels as k
+    rng = np.random.default_rng(2024)
+    shapes = [(1, 1, 1), (2, 1, 3), (7, 2, 1), (33, 3, 5), (129, 5, 31), (257, 8, 32), (100, 9, 33), (64, 16, 100),
+              (301, 17, 191), (1000, 23, 192), (17000, 13, 200), (515, 31, 65), (130, 33, 40), (99, 47, 129),
+              (260, 64, 70), (1, 30, 100), (4097, 30, 257)]
+    for n, D, M in shapes:
+        vf = {"X_ctrl": rng.normal(size=(M, D)), "beta": 0.7 / D, "C": rng.normal(size=(M, D)) / np.sqrt(M)}
+        x = rng.normal(size=(n, D))
+        what = (n, D, M)
+        assert rel(pkg.con_K(x, vf["X_ctrl"], vf["beta"]).reshape(n, M), o.gauss_kernel(x, vf["X_ctrl"], vf["beta"]).reshape(n, M)) < 1e-13, what
+        assert rel(pkg.vector_field_function(x, vf).reshape(n, D), o.field_eval(x, vf).reshape(n, D)) < 1e-12, what
+        Jr = o.jacobian(x, vf).reshape(D, D, n)
+        J = pkg.Jacobian_rkhs_gaussian(x, vf).reshape(D, D, n)
+        assert rel(J, Jr) < 1e-11, what
+        Jd = _np(k.jacobian(x, vf["X_ctrl"], vf["beta"], vf["C"]))
+        assert rel(Jd, Jr) < 1e-11, what
+        f_jac, func = pkg.RkhsJacobian(vf), pkg.RkhsField(vf)
+        if n > 1:       # the reference's own single-row conventions are covered by test_calculus_fixed_C
+            assert rel(pkg.compute_divergence(f_jac, x), o.divergence(x, vf)) < 1e-11, what
+            a, am = pkg.compute_acceleration(func, f_jac, x)
+            _, _, ar, amr = o.acceleration(x, vf)
+            assert rel(a, ar) < 1e-10 and rel(am, amr) < 1e-10, what
+            # curvature = (a |v|^2 - v (v.a)) / |v|^4 cancels to an exact zero when a is parallel to v (D = 1, M = 1):
+            # compare on the scale of its two terms, |a| / |v|^2
+            c, cm = pkg.compute_curvature(func, f_jac, x)
+            cr, cmr = o.curvature(x, vf)
+            scale = np.max(ar / np.sum(o.field_eval(x, vf).reshape(n, D) ** 2, 1))
+            assert np.max(np.abs(c - cr)) <= 1e-9 * scale and np.max(np.abs(cm - cmr)) <= 1e-9 * scale, what
+        det = pkg.jacobian_det(Jr)
+        detr = o.jacobian_det(Jr)
+        # perturbation bound of a determinant: n eps cond |det|, and for (near-)singular matrices n eps sigma_max^n
+        cond = np.array([np.linalg.cond(Jr[:, :, i]) for i in range(n)])
+        smax = np.array([np.linalg.norm(Jr[:, :, i], 2) for i in range(n)])
+        with np.errstate(invalid="ignore", over="ignore"):
+            bound = 100 * D * 2.3e-16 * (np.where(np.isfinite(cond), cond, 0.0) * np.abs(detr) + smax ** D)
+        assert np.all(np.abs(det - detr) <= bound + 1e-300), what
+        if D <= 24 and n <= 300:
+            H = pkg.Hessian_rkhs_gaussian(x[:9], vf).reshape(D, D, D, -1)
+            Hr = o.hessian_cells(x[:9], vf)
+            assert rel(H, Hr) < 1e-11, what
+            assert rel(pkg.laplacian_rkhs(x[:9], vf).reshape(D, -1), o.laplacian_of(Hr)) < 1e-11, what
+        G = min(5 + D, 40)
+        Q = rng.normal(size=(G, D))
+        Jg = pkg.transform_jacobian(Jr, Q, Q)
+        Jgr = o.gene_jacobian(Jr, Q, Q)
+        assert Jg.dtype == np.float32 and Jg.shape == Jgr.shape, what
+        assert np.max(np.abs(Jg.astype(np.float64) - Jgr.astype(np.float64))) <= 2.5e-7 * np.max(np.abs(Jgr)), what
+        assert rel(pkg.vector_transformation(x, Q), o.to_gene_space(x, Q)) < 1e-13, what
+
+
 def test_edge_cases(pkg):
     rng = np.random.default_rng(1)
     vf = {"X_ctrl": rng.normal(size=(7, 3)), "beta": 0.3, "C": rng.normal(size=(7, 3))}
