@@ -119,14 +119,14 @@ __global__ void k_pad_c(const double* __restrict__ C, int M, int D, double* __re
 // CTA = 128 cells (16 per warp), contraction over ctrl points in chunks of 32 through a cp.async ring.
 template <int NT>
 struct uv_cfg {
-    static constexpr int DP = NT * 8, KC = 32, STAGES = 3;
+    static constexpr int DP = NT * 8, KC = 32, STAGES = 2;   // 92 KB per CTA: two CTAs (16 warps) per SM
     static constexpr int LDU = KC + 4;                             // == 4 (mod 16)
     static constexpr int LDC = ((DP + 15) / 16) * 16 + 4;          // == 4 (mod 16)
     static constexpr size_t SMEM = sizeof(double) * (size_t)STAGES * (UV_CELLS * LDU + KC * LDC);
 };
 
 template <int NT>
-__global__ void __launch_bounds__(256) k_update_v(const double* __restrict__ UY, const double* __restrict__ Cp,
+__global__ void __launch_bounds__(256, 2) k_update_v(const double* __restrict__ UY, const double* __restrict__ Cp,
                                                   const double* __restrict__ P, double minP, int64_t N, int D, int M,
                                                   int W, double* __restrict__ V, double* __restrict__ r2,
                                                   double* __restrict__ part, const int* __restrict__ done) {
