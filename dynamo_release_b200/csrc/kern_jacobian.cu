@@ -87,8 +87,8 @@ k_jacobian_gemm(const __grid_constant__ CUtensorMap mapT, const __grid_constant_
         // ---------------- producer: one thread ----------------
         if (lane != 0) return;
         for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int t = (int)(item % n_tiles);
             const int cb = (int)(item / n_tiles);
+            const int t = (int)((item % n_tiles + cb) % n_tiles);     // rotated: see the consumer side
             for (int ks = 0; ks < k_stages; ++ks) {
                 mbar_wait(&empty[rs.stage], rs.phase ^ 1u);
                 const unsigned sb = smem_u32(ring) + rs.stage * JG_STAGE_B, bar = smem_u32(&full[rs.stage]);
@@ -128,17 +128,25 @@ k_jacobian_gemm(const __grid_constant__ CUtensorMap mapT, const __grid_constant_
     const int n_i = jg_ni(D);
 
     for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int t = (int)(item % n_tiles);
+        // the row tile is rotated by the cell block so that every CTA meets all tiles equally often (the grid stride
+        // and n_tiles share factors, and the last tile is cheaper than the others)
         const int64_t cb = item / n_tiles;
+        const int t = (int)((item % n_tiles + cb) % n_tiles);
         double acc[4][4][2];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
             for (int q = 0; q < 4; ++q) acc[i][q][0] = acc[i][q][1] = 0.0;
 
+        // rows of this tile that exist: the last tile usually holds fewer groups (D = 30: 2 of 4 -> 62 rows), and a
+        // warp whose 32 rows are all padding only keeps the ring protocol going; warp % 4 = wj, so every scheduler
+        // keeps the same number of working warps and the tile costs the DMMA pipe only its real rows
+        const int rows_here = min(n_i, D - t * n_i) * (D + 1);
+        const bool active = wi * 32 < rows_here;
         for (int ks = 0; ks < k_stages; ++ks) {
             mbar_wait(&full[rs.stage], rs.phase);
             const unsigned char* sb = ring + rs.stage * JG_STAGE_B;
+            if (active)
 #pragma unroll
             for (int sk = 0; sk < 8; ++sk) {
                 const int sp = sk & 1;
