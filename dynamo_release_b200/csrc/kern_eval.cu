@@ -20,6 +20,61 @@ __global__ void __launch_bounds__(256) k_kernel_matrix(const double* __restrict_
     __shared__ double cs[K1_DC][K1_T + 4];
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
     const int64_t n0 = (int64_t)blockIdx.x * K1_T;
+    if (D <= K1_DC) {
+        // one chunk of dimensions: the cell tile is staged once, and the next control-point tile is fetched into
+        // registers while the current one is being used
+        for (int e = threadIdx.x; e < K1_T * K1_DC; e += 256) {
+            const int r = e / K1_DC, d = e % K1_DC;
+            const int64_t gn = n0 + r;
+            xs[d][r] = (gn < n && d < D) ? x[gn * D + d] : 0.0;
+        }
+        double pre[K1_T * K1_DC / 256];
+#pragma unroll
+        for (int q = 0; q < K1_T * K1_DC / 256; ++q) {
+            const int e = threadIdx.x + q * 256, r = e / K1_DC, d = e % K1_DC;
+            pre[q] = (r < M && d < D) ? Xc[(int64_t)r * D + d] : 0.0;
+        }
+        for (int m0 = 0; m0 < M; m0 += K1_T) {
+            __syncthreads();
+#pragma unroll
+            for (int q = 0; q < K1_T * K1_DC / 256; ++q) {
+                const int e = threadIdx.x + q * 256;
+                cs[e % K1_DC][e / K1_DC] = pre[q];
+            }
+            __syncthreads();
+            if (m0 + K1_T < M) {
+#pragma unroll
+                for (int q = 0; q < K1_T * K1_DC / 256; ++q) {
+                    const int e = threadIdx.x + q * 256, r = m0 + K1_T + e / K1_DC, d = e % K1_DC;
+                    pre[q] = (r < M && d < D) ? Xc[(int64_t)r * D + d] : 0.0;
+                }
+            }
+            double acc[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
+            for (int d = 0; d < D; ++d) {
+                double xv[4], cv[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { xv[i] = xs[d][ty * 4 + i]; cv[i] = cs[d][tx * 4 + i]; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { double t = xv[i] - cv[j]; acc[i][j] = fma(t, t, acc[i][j]); }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int64_t gn = n0 + ty * 4 + i;
+                if (gn >= n) continue;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int gm = m0 + tx * 4 + j;
+                    if (gm < M) K[gn * ldk + gm] = exp(-beta * acc[i][j]);
+                }
+            }
+        }
+    } else
     for (int m0 = 0; m0 < M; m0 += K1_T) {
         double acc[4][4];
 #pragma unroll
