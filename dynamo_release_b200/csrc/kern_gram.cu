@@ -54,7 +54,11 @@ __host__ __device__ inline int gv_ks(int v) { return v == GV_FULL ? 1 : v == GV_
 // relative cost of one 32-cell step (DMMA count x a penalty for the smaller shapes, calibrated on B200 with
 // DVF_GRAM_ONLY, tools/gram_tune.py)
 static double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.1, 128.0 * 1.05, 64.0 * 1.1, 48.0 * 1.15, 32.0 * 1.25, 16.0 * 1.6};
-static double g_diag_factor = 0.78;
+// parts schedule: plain DMMA counts down to the 24-row strips -- without accumulator swaps those shapes cost what they
+// compute (swept on B200 with tools/gram_cost_sweep.sh: 9.80-9.83 ms on a plateau around these values, 10.4 ms with
+// the bundle table); the two thinnest strips keep their penalty (M = 100: 1.36 ms with it, 1.69 ms without)
+static double kPartCost[GV_COUNT] = {256.0, 64.0, 128.0, 64.0, 48.0, 32.0 * 1.25, 16.0 * 1.6};
+static double g_diag_factor = 0.75;
 static int g_parts = -1, g_sb_parts = 512;   // -1: planner decides, 0: bundles only, 1: parts whenever possible
 static int g_force_G = 0, g_sb = 64, g_lag = 0, g_only = -1, g_debug = 0;   // sb, lag: measured on B200
 static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not part of the ABI
@@ -64,6 +68,9 @@ static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not p
     if (const char* e = getenv("DVF_GRAM_COST"))
         sscanf(e, "%lf,%lf,%lf,%lf,%lf,%lf,%lf", &kVarCost[0], &kVarCost[1], &kVarCost[2], &kVarCost[3], &kVarCost[4],
                &kVarCost[5], &kVarCost[6]);
+    if (const char* e = getenv("DVF_GRAM_PCOST"))
+        sscanf(e, "%lf,%lf,%lf,%lf,%lf,%lf,%lf", &kPartCost[0], &kPartCost[1], &kPartCost[2], &kPartCost[3], &kPartCost[4],
+               &kPartCost[5], &kPartCost[6]);
     if (const char* e = getenv("DVF_GRAM_G")) g_force_G = atoi(e);
     if (const char* e = getenv("DVF_GRAM_DIAG")) g_diag_factor = atof(e);
     if (const char* e = getenv("DVF_GRAM_PARTS")) g_parts = atoi(e);
@@ -398,6 +405,7 @@ struct gram_host_plan {
 
 // a diagonal 64 x 64 tile runs 12 of its 16 warps
 static double tile_cost(const gram_tile& tl) { return kVarCost[tl.variant] * (tl.diag ? g_diag_factor : 1.0); }
+static double part_cost(const gram_tile& tl) { return kPartCost[tl.variant] * (tl.diag ? g_diag_factor : 1.0); }
 
 static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& hp) {
     read_tuning_env();
@@ -467,21 +475,26 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
     double parts_eff = 0.0;
     if (nt <= n_sms && n_steps >= 4 * (int64_t)n_sms && g_parts != 0) {
         std::vector<int> p(nt, 1);
+        double ptotal = 0.0;
+        for (int i = 0; i < nt; ++i) ptotal += part_cost(hp.tiles[i]);
         for (int used = nt; used < n_sms; ++used) {
             int arg = 0;
             double worst = -1.0;
             for (int i = 0; i < nt; ++i) {
-                const double c = tile_cost(hp.tiles[i]) / p[i];
+                const double c = part_cost(hp.tiles[i]) / p[i];
                 if (c > worst) { worst = c; arg = i; }
             }
             p[arg]++;
         }
         double worst = 0.0;
         int used = 0;
-        for (int i = 0; i < nt; ++i) { worst = std::max(worst, tile_cost(hp.tiles[i]) / p[i]); used += p[i]; }
-        parts_eff = total / (n_sms * worst);
-        // the bundle schedule reloads and stores its accumulators at every block: measured ~5 % on B200
-        if (g_parts > 0 || parts_eff > 0.95 * best_eff) {
+        for (int i = 0; i < nt; ++i) { worst = std::max(worst, part_cost(hp.tiles[i]) / p[i]); used += p[i]; }
+        parts_eff = ptotal / (n_sms * worst);
+        // measured: parts wins clearly where the bundles are unbalanced (M = 500: 0.957 vs 0.881 predicted, 9.8 vs
+        // 11.0 ms) and loses by ~3 % where both balance well (M = 1000: 0.953 vs 0.972, 37.0 vs 35.9 ms)
+        // (the bundle prediction ignores the accumulator swaps of multi-tile CTAs: with few tiles parts always won,
+        // 100k x (100+30): 0.35 vs 1.28 ms, 500k x (300+30): 2.43 vs 2.63 ms)
+        if (g_parts > 0 || nt <= 32 || parts_eff > best_eff + 0.01) {
             hp.use_parts = true;
             hp.part_off.assign(nt + 1, 0);
             for (int i = 0; i < nt; ++i) {

@@ -21,31 +21,6 @@ struct solve_args {
     double* L; int ldl; double* C; int* info; const int* done;
 };
 
-// Cholesky of the 32 x 32 diagonal block (identity-padded past nb) by ONE warp: lane i keeps row i in registers, the
-// pivot column travels by shuffles.  Same operations per element as the textbook right-looking loop (divide by the
-// square root, one fused multiply-subtract per update), without its three CTA barriers per column.
-__device__ __noinline__ void chol32_warp(double (*Dg)[SV_NB + 1], int nb, int k0, int* info, bool report) {
-    const int lane = threadIdx.x & 31;
-    double r[SV_NB];
-#pragma unroll
-    for (int j = 0; j < SV_NB; ++j) r[j] = Dg[lane][j];
-#pragma unroll
-    for (int j = 0; j < SV_NB; ++j) {
-        const double d = __shfl_sync(0xffffffffu, r[j], j);
-        if (report && lane == 0 && j < nb && !(d > 0.0)) atomicCAS(info, 0, k0 + j + 1);
-        const double l = sqrt(d);
-        if (lane > j) r[j] /= l;
-        if (lane == j) r[j] = l;
-#pragma unroll
-        for (int c = j + 1; c < SV_NB; ++c) {
-            const double lcj = __shfl_sync(0xffffffffu, r[j], c);
-            if (lane >= c) r[c] = fma(-r[j], lcj, r[c]);
-        }
-    }
-#pragma unroll
-    for (int j = 0; j < SV_NB; ++j) Dg[lane][j] = r[j];
-}
-
 __global__ void __launch_bounds__(256) k_chol_solve(solve_args a) {
     cg::grid_group grid = cg::this_grid();
     if (a.done && *a.done) return;            // uniform over the grid: no sync is skipped by a subset
@@ -78,8 +53,20 @@ __global__ void __launch_bounds__(256) k_chol_solve(solve_args a) {
             Dg[i][j] = (i < nb && j <= i) ? L[(int64_t)(k0 + i) * ldl + k0 + j] : (i == j ? 1.0 : 0.0);
         }
         __syncthreads();
-        if (tid < 32) chol32_warp(Dg, nb, k0, a.info, blockIdx.x == 0);
-        __syncthreads();
+        for (int j = 0; j < nb; ++j) {
+            const double d = Dg[j][j];
+            __syncthreads();
+            if (!(d > 0.0) && blockIdx.x == 0 && tid == 0) atomicCAS(a.info, 0, k0 + j + 1);
+            const double l = sqrt(d);
+            if (tid > j && tid < nb) Dg[tid][j] /= l;
+            if (tid == j) Dg[j][j] = l;
+            __syncthreads();
+            for (int e = tid; e < nb * nb; e += nthr) {
+                const int i = e / nb, c = e % nb;
+                if (c > j && i >= c) Dg[i][c] -= Dg[i][j] * Dg[c][j];
+            }
+            __syncthreads();
+        }
         if (blockIdx.x == 0)
             for (int e = tid; e < nb * nb; e += nthr) {
                 const int i = e / nb, j = e % nb;
