@@ -59,7 +59,7 @@ static double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.1, 128.0 * 1.05, 64.0 * 1.1,
 // the bundle table); the two thinnest strips keep their penalty (M = 100: 1.36 ms with it, 1.69 ms without)
 static double kPartCost[GV_COUNT] = {256.0, 64.0, 128.0, 64.0, 48.0, 32.0 * 1.25, 16.0 * 1.6};
 static double g_diag_factor = 0.75;
-static int g_parts = -1, g_sb_parts = 512;   // -1: planner decides, 0: bundles only, 1: parts whenever possible
+static int g_parts = -1, g_sb_parts = 2048;   // block length swept on B200: 256: 10.08, 512: 9.81, 1024: 9.66, 2048: 9.60 ms   // -1: planner decides, 0: bundles only, 1: parts whenever possible
 static int g_force_G = 0, g_sb = 64, g_lag = 0, g_only = -1, g_debug = 0;   // sb, lag: measured on B200
 static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not part of the ABI
     static bool done = false;

@@ -5,6 +5,8 @@
 // exact arithmetic with an error bound of cond(lhs) eps instead of cond(lhs)^2 eps ("solver").
 // One cooperative launch: the D right-hand-side columns ride along as D extra rows of the panel, so the
 // forward substitution costs nothing extra; the backward substitution follows block by block.
+#include <algorithm>
+#include <cstdlib>
 #include <cooperative_groups.h>
 #include "common.cuh"
 
@@ -179,9 +181,11 @@ int solve_run(const double* G, int64_t ldg, const double* Kc, int M, int D, doub
         if (max_grid == 0) { set_error("k_chol_solve cannot be made resident"); return DVF_ERR_CUDA; }
     }
     int grid = max_grid;
-    const int want = (M + D + 31) / 32 * 2;          // more CTAs than this only add grid-sync cost
+    const int want = (M + D + 31) / 32 * 4;          // more CTAs than this only add grid-sync cost (tools/solve_tune.py)
     if (grid > want) grid = want < 8 ? 8 : want;
     if (grid > max_grid) grid = max_grid;
+    static const char* force = getenv("DVF_SOLVE_GRID");   // developer knob (tools/solve_tune.py)
+    if (force && atoi(force) > 0) grid = std::min(atoi(force), max_grid);
     void* params[] = {&a};
     ++g_launch_count;
     DVF_CUDA(cudaLaunchCooperativeKernel((void*)k_chol_solve, dim3(grid), dim3(256), params, 0, st));
