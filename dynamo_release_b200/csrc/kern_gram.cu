@@ -59,7 +59,9 @@ static double kVarCost[GV_COUNT] = {256.0, 64.0 * 1.1, 128.0 * 1.05, 64.0 * 1.1,
 // the bundle table); the two thinnest strips keep their penalty (M = 100: 1.36 ms with it, 1.69 ms without)
 static double kPartCost[GV_COUNT] = {256.0, 64.0, 128.0, 64.0, 48.0, 32.0 * 1.25, 16.0 * 1.6};
 static double g_diag_factor = 0.75;
-static int g_parts = -1, g_sb_parts = 2048;   // block length swept on B200: 256: 10.08, 512: 9.81, 1024: 9.66, 2048: 9.60 ms   // -1: planner decides, 0: bundles only, 1: parts whenever possible
+// g_parts: -1 planner decides, 0 bundles only, 1 parts whenever possible.  g_sb_parts: block length in stages; 0 = the
+// planner picks a length near 512 that the part counts divide (see build_host_plan)
+static int g_parts = -1, g_sb_parts = 0;
 static int g_force_G = 0, g_sb = 64, g_lag = 0, g_only = -1, g_debug = 0;   // sb, lag: measured on B200
 static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not part of the ABI
     static bool done = false;
@@ -74,7 +76,7 @@ static void read_tuning_env() {   // developer knobs (tools/gram_tune.py); not p
     if (const char* e = getenv("DVF_GRAM_G")) g_force_G = atoi(e);
     if (const char* e = getenv("DVF_GRAM_DIAG")) g_diag_factor = atof(e);
     if (const char* e = getenv("DVF_GRAM_PARTS")) g_parts = atoi(e);
-    if (const char* e = getenv("DVF_GRAM_SBP")) g_sb_parts = std::max(8, atoi(e));
+    if (const char* e = getenv("DVF_GRAM_SBP")) g_sb_parts = std::max(0, atoi(e));
     if (const char* e = getenv("DVF_GRAM_SB")) g_sb = std::max(1, atoi(e));
     if (const char* e = getenv("DVF_GRAM_LAG")) g_lag = atoi(e);       // blocks a producer may run ahead of its group
     if (const char* e = getenv("DVF_GRAM_ONLY")) g_only = atoi(e);     // timing experiments: keep one tile variant
@@ -399,6 +401,7 @@ struct gram_host_plan {
     int n_groups = 1;
     // parts schedule (used when it is predicted to be faster)
     bool use_parts = false;
+    int sb_parts = 512;
     std::vector<gram_part> parts;
     std::vector<int> part_off;
 };
@@ -502,11 +505,27 @@ static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& 
                 for (int k = 0; k < p[i]; ++k) hp.parts.push_back(gram_part{i, k, p[i], 0});
             }
             hp.part_off[nt] = (int)hp.parts.size();
+            // Block length.  Part k of a tile takes the stages [len k / p, len (k+1) / p) of every block, and all CTAs
+            // meet at every block start, so a block costs its LARGEST part: with 512 stages and p = 15 that is 35
+            // stages where 34.1 are due (2.5 %, paid 61 times; measured 9.81 ms against 9.54 ms with 2048-stage
+            // blocks, whose 300 MB no longer fit the L2: 12.3 GB of DRAM traffic per launch instead of 5.0 GB).
+            // Pick the length in [448, 704] that the part counts divide best: same speed, blocks stay L2-sized.
+            hp.sb_parts = 512;
+            if (g_sb_parts > 0) hp.sb_parts = g_sb_parts;
+            else {
+                double best_loss = 1e30;
+                for (int sb = 448; sb <= 704; sb += 4) {
+                    double loss = 0.0;
+                    for (int i = 0; i < nt; ++i) loss = std::max(loss, (double)((sb + p[i] - 1) / p[i]) * p[i] / sb);
+                    if (loss < best_loss - 1e-9) { best_loss = loss; hp.sb_parts = sb; }
+                }
+            }
             (void)used;
         }
     }
     if (g_debug) {
-        fprintf(stderr, "[gram plan] parts schedule: eff=%.3f %s\n", parts_eff, hp.use_parts ? "(used)" : "(not used)");
+        fprintf(stderr, "[gram plan] parts schedule: eff=%.3f %s, block of %d stages\n", parts_eff,
+                hp.use_parts ? "(used)" : "(not used)", hp.sb_parts);
         int cnt[GV_COUNT] = {0};
         for (auto& tl : hp.tiles) cnt[tl.variant]++;
         fprintf(stderr, "[gram plan] N=%lld M=%d D=%d tiles=%d (full %d half %d s8 %d s4 %d s3 %d s2 %d s1 %d) bundles=%d groups=%d eff=%.3f\n",
@@ -528,8 +547,8 @@ gram_plan make_gram_plan(int64_t N, int D, int M) {
     pl.n_ctas = pl.n_bundles * pl.n_groups;
     pl.use_parts = hp.use_parts ? 1 : 0;
     pl.n_parts = (int)hp.parts.size();
-    pl.sb_parts = g_sb_parts;
-    pl.n_counters = (int)(((N + GR_KC - 1) / GR_KC + g_sb_parts - 1) / g_sb_parts) + 1;
+    pl.sb_parts = hp.sb_parts;
+    pl.n_counters = (int)(((N + GR_KC - 1) / GR_KC + hp.sb_parts - 1) / hp.sb_parts) + 1;
     size_t o = 0;
     pl.off_tiles = o;  o += al256(sizeof(gram_tile) * hp.tiles.size());
     pl.off_boff = o;   o += al256(sizeof(int) * hp.bundle_off.size());
