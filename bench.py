@@ -28,7 +28,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-GRAM_DRAM_BYTES_NCU = 5.13e9    # k_gram_parts: 5.12 GB read + 7 MB written per launch (ncu --set full, profiles/ncu_k_gram_parts_r01_details.txt)
+GRAM_DRAM_BYTES_NCU = 4.85e9    # k_gram_parts: 4.84 GB read + 7 MB written per launch (ncu --set full, profiles/ncu_k_gram_parts_r01_details.txt)
 FP64_PEAK_TFLOPS = 37.1   # DMMA m8n8k4 chain measured on this pool's B200 (tools/fp64_peak.cu, profiles/fp64_peak_r01.json)
 
 
