@@ -282,6 +282,138 @@ __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64
     }
 }
 
+// K7 for D > 32: x, v and a of one cell no longer fit the register file of one thread (D = 50: 696 bytes of spills in
+// the kernel above), so TWO adjacent lanes share a cell, each holding HD = DP / 2 of its dimensions; the partial
+// distances and dot products are completed with one shuffle each.  Same arithmetic per dimension as k_dac; the two
+// halves of a sum are added lower half first.
+template <int HD>
+__global__ void __launch_bounds__(128) k_dac2(const double* __restrict__ x, int64_t n, int D,
+                                              const double* __restrict__ Xc, int M, double beta,
+                                              const double* __restrict__ C, int formula, double* __restrict__ v_out,
+                                              double* __restrict__ div_out, double* __restrict__ acc_out,
+                                              double* __restrict__ accn_out, double* __restrict__ curv_out,
+                                              double* __restrict__ curvn_out) {
+    constexpr int DP = 2 * HD;
+    __shared__ double cs[ev_chunk<DP>::MC * DP];
+    __shared__ double Cs[ev_chunk<DP>::MC * DP];
+    const int64_t cell = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 1;
+    const int h = threadIdx.x & 1, d0 = h * HD;
+    const bool live = cell < n;
+    double xr[HD], vr[HD];
+#pragma unroll
+    for (int d = 0; d < HD; ++d) { xr[d] = (live && d0 + d < D) ? x[cell * D + d0 + d] : 0.0; vr[d] = 0.0; }
+    double div = 0.0;
+    for (int m0 = 0; m0 < M; m0 += ev_chunk<DP>::MC) {
+        const int mc = min(ev_chunk<DP>::MC, M - m0);
+        __syncthreads();
+        load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
+        __syncthreads();
+        for (int m = 0; m < mc; ++m) {
+            const double* cm = cs + m * DP + d0;
+            const double* Cm = Cs + m * DP + d0;
+            double d2a = 0.0, d2b = 0.0, t2a = 0.0, t2b = 0.0;
+#pragma unroll
+            for (int d = 0; d < HD; d += 2) {
+                double ta = xr[d] - cm[d], tb = xr[d + 1] - cm[d + 1];
+                d2a = fma(ta, ta, d2a);
+                d2b = fma(tb, tb, d2b);
+                t2a = fma(ta, Cm[d], t2a);
+                t2b = fma(tb, Cm[d + 1], t2b);
+            }
+            double d2 = d2a + d2b, t2 = t2a + t2b;
+            const double d2o = __shfl_xor_sync(0xffffffffu, d2, 1), t2o = __shfl_xor_sync(0xffffffffu, t2, 1);
+            d2 = h ? d2o + d2 : d2 + d2o;          // lower half first on both lanes: identical k
+            t2 = h ? t2o + t2 : t2 + t2o;
+            const double k = exp(-beta * d2);
+            div = fma(k, t2, div);
+#pragma unroll
+            for (int d = 0; d < HD; ++d) vr[d] = fma(k, Cm[d], vr[d]);
+        }
+    }
+    div *= -2.0 * beta;
+    const bool need_acc = acc_out || accn_out || curv_out || curvn_out;
+    double ar[HD];
+#pragma unroll
+    for (int d = 0; d < HD; ++d) ar[d] = 0.0;
+    if (need_acc) {
+        for (int m0 = 0; m0 < M; m0 += ev_chunk<DP>::MC) {
+            const int mc = min(ev_chunk<DP>::MC, M - m0);
+            __syncthreads();
+            load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
+            __syncthreads();
+            for (int m = 0; m < mc; ++m) {
+                const double* cm = cs + m * DP + d0;
+                const double* Cm = Cs + m * DP + d0;
+                double d2a = 0.0, d2b = 0.0, sa = 0.0, sb = 0.0;
+#pragma unroll
+                for (int d = 0; d < HD; d += 2) {
+                    double ta = xr[d] - cm[d], tb = xr[d + 1] - cm[d + 1];
+                    d2a = fma(ta, ta, d2a);
+                    d2b = fma(tb, tb, d2b);
+                    sa = fma(ta, vr[d], sa);
+                    sb = fma(tb, vr[d + 1], sb);
+                }
+                double d2 = d2a + d2b, sv = sa + sb;
+                const double d2o = __shfl_xor_sync(0xffffffffu, d2, 1), svo = __shfl_xor_sync(0xffffffffu, sv, 1);
+                d2 = h ? d2o + d2 : d2 + d2o;
+                sv = h ? svo + sv : sv + svo;
+                const double ks = exp(-beta * d2) * sv;
+#pragma unroll
+                for (int d = 0; d < HD; ++d) ar[d] = fma(ks, Cm[d], ar[d]);
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < HD; ++d) ar[d] *= -2.0 * beta;
+    }
+    // per-cell scalars need both halves (every lane of the warp takes part in the shuffles)
+    double vv = 0.0, va = 0.0, aa = 0.0;
+#pragma unroll
+    for (int d = 0; d < HD; ++d) { vv = fma(vr[d], vr[d], vv); va = fma(vr[d], ar[d], va); aa = fma(ar[d], ar[d], aa); }
+    {
+        const double vvo = __shfl_xor_sync(0xffffffffu, vv, 1), vao = __shfl_xor_sync(0xffffffffu, va, 1),
+                     aao = __shfl_xor_sync(0xffffffffu, aa, 1);
+        vv = h ? vvo + vv : vv + vvo;
+        va = h ? vao + va : va + vao;
+        aa = h ? aao + aa : aa + aao;
+    }
+    double kk = 0.0;
+    double cr[HD];
+    const double nv = sqrt(vv);
+    if (formula == 2) {
+        const double den = (nv * nv) * (nv * nv);
+#pragma unroll
+        for (int d = 0; d < HD; ++d) { cr[d] = (ar[d] * vv - vr[d] * va) / den; kk = fma(cr[d], cr[d], kk); }
+    }
+    {
+        const double kko = __shfl_xor_sync(0xffffffffu, kk, 1);
+        kk = h ? kko + kk : kk + kko;
+    }
+    if (!live) return;
+    if (v_out) {
+#pragma unroll
+        for (int d = 0; d < HD; ++d)
+            if (d0 + d < D) v_out[cell * D + d0 + d] = vr[d];
+    }
+    if (div_out && h == 0) div_out[cell] = div;
+    if (!need_acc) return;
+    if (acc_out) {
+#pragma unroll
+        for (int d = 0; d < HD; ++d)
+            if (d0 + d < D) acc_out[cell * D + d0 + d] = ar[d];
+    }
+    if (accn_out && h == 0) accn_out[cell] = sqrt(aa);
+    if (formula == 2) {
+        if (curv_out) {
+#pragma unroll
+            for (int d = 0; d < HD; ++d)
+                if (d0 + d < D) curv_out[cell * D + d0 + d] = cr[d];
+        }
+        if (curvn_out && h == 0) curvn_out[cell] = sqrt(kk);
+    } else if (curvn_out && h == 0) {
+        curvn_out[cell] = sqrt(vv * aa) / (nv * nv * nv);
+    }
+}
+
 template <typename F>
 static int dispatch_dp(int D, F&& f) {
     if (D <= 2) return f(std::integral_constant<int, 2>());
@@ -360,6 +492,20 @@ extern "C" int dvf_div_acc_curv(const double* x, int64_t n, int D, const double*
     DVF_ARG(C, "NULL pointer");
     DVF_ARG(formula == 1 || formula == 2, "formula must be 1 or 2");
     if (n == 0) return DVF_OK;
+    if (D > 32) {   // two lanes per cell (k_dac2): HD = half of D rounded up to the next multiple of 4
+        const unsigned blocks = (unsigned)((2 * n + 127) / 128);
+        auto launch = [&](auto hd) {
+            constexpr int HD = decltype(hd)::value;
+            k_dac2<HD><<<blocks, 128, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, formula, v, div, acc, acc_norm, curv,
+                                                               curv_norm);
+        };
+        if (D <= 40) launch(std::integral_constant<int, 20>());
+        else if (D <= 48) launch(std::integral_constant<int, 24>());
+        else if (D <= 56) launch(std::integral_constant<int, 28>());
+        else launch(std::integral_constant<int, 32>());
+        DVF_LAUNCH_CHECK();
+        return DVF_OK;
+    }
     return dispatch_dp(D, [&](auto dp) {
         constexpr int DP = decltype(dp)::value;
         k_dac<DP><<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, formula, v, div,
