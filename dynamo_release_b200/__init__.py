@@ -4,11 +4,12 @@ Drop-in names (same signatures as dynamo.vectorfield.scVectorField / dynamo.vect
     SparseVFC, SvcVectorField, con_K, vector_field_function, Jacobian_rkhs_gaussian,
     Jacobian_rkhs_gaussian_parallel, compute_divergence, compute_acceleration, compute_curvature,
     elementwise_jacobian_transformation, subset_jacobian_transformation, transform_jacobian,
-    vector_transformation, vecfld_from_adata
+    vector_transformation, vecfld_from_adata, integrate_vf_ivp (dynamo.prediction.utils)
 `install()` (patch.py) rebinds them inside an importable dynamo.  There is no CPU fallback.
 """
 from .sparsevfc import SparseVFC, fit_em  # noqa: F401
 from .svc import SvcVectorField, vecfld_from_adata  # noqa: F401
+from .integrate import DenseSolution, ScaledRkhsField, integrate_vf_ivp, solve_ivp_batch  # noqa: F401
 from .vf import (  # noqa: F401
     Hessian_rkhs_gaussian,
     Laplacian,

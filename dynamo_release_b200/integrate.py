@@ -1,0 +1,279 @@
+"""Batched integration of initial states through the RKHS vector field.
+
+Drop-in for reference prediction/utils.py:62-259 (`integrate_vf_ivp`) and BaseVectorField.integrate
+(vectorfield/scVectorField.py:721-784).  The reference runs scipy.integrate.solve_ivp once per cell, every
+right-hand-side call being a NumPy `vector_field_function`; here every trajectory is one CTA of K11
+(csrc/kern_ivp.cu, dvf_integrate_rk45) that runs the same adaptive Dormand-Prince 5(4) integration, terminal event
+and dense output on the device.  The sampling of the finished trajectories (arc length / log space / uniform indices)
+is the reference's host-side bookkeeping, restated below with the same NumPy / SciPy calls it makes.
+
+The field must be this package's RKHS field (an object carrying `vf_dict`, e.g. SvcVectorField.func); there is no
+CPU fallback for arbitrary Python callables.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+from scipy.interpolate import interp1d
+
+from . import _lib
+from .device import dev, lib, ptr, stream_ptr
+from .vf import RkhsField, _vf_parts
+
+RTOL, ATOL, REST_TOL = 1e-3, 1e-6, 1e-5     # solve_ivp defaults; event threshold of prediction/utils.py:107
+_BYTES_PER_LAUNCH = 1 << 30                 # trajectories are integrated in groups whose outputs fit this
+
+
+class ScaledRkhsField(RkhsField):
+    """x -> scale * f(x): what BaseVectorField.integrate binds when `func` is unset (scVectorField.py:764-766)."""
+
+    def __init__(self, vf_dict, scale=1.0):
+        super().__init__(vf_dict)
+        self.scale = scale
+
+    def __call__(self, x, **kw):
+        return self.scale * super().__call__(x, **kw)
+
+
+class DenseSolution:
+    """The continuous solution of one trajectory: evaluates like scipy's OdeSolution over RkDenseOutput pieces
+    (scipy/integrate/_ivp/common.py, rk.py) but for all requested times at once."""
+
+    def __init__(self, ts, ys, Q, h=None):
+        ts = np.asarray(ts)
+        d = np.diff(ts)
+        if not ((ts.size == 2 and ts[0] == ts[-1]) or np.all(d > 0) or np.all(d < 0)):
+            raise ValueError("`ts` must be strictly increasing or decreasing.")
+        self.ts, self.ys, self.Q, self.h = ts, ys, Q, (d if h is None else np.asarray(h))
+        self.n_segments = len(d)
+        self.ascending = bool(ts[-1] >= ts[0])
+        self.t_min, self.t_max = (ts[0], ts[-1]) if self.ascending else (ts[-1], ts[0])
+
+    def __call__(self, t):
+        t = np.asarray(t, dtype=np.float64)
+        tt = np.atleast_1d(t)
+        if self.ascending:
+            seg = np.searchsorted(self.ts, tt, side="left") - 1
+            seg = np.clip(seg, 0, self.n_segments - 1)
+        else:
+            seg = np.searchsorted(self.ts[::-1], tt, side="right") - 1
+            seg = self.n_segments - 1 - np.clip(seg, 0, self.n_segments - 1)
+        h = self.h[seg]
+        x = (tt - self.ts[seg]) / h
+        p = np.cumprod(np.tile(x, (4, 1)), axis=0)                       # x, x^2, x^3, x^4
+        Qs = self.Q[seg]                                                  # (nt, D, 4)
+        y = ((Qs[:, :, 0] * p[0][:, None] + Qs[:, :, 1] * p[1][:, None]) + Qs[:, :, 2] * p[2][:, None]) \
+            + Qs[:, :, 3] * p[3][:, None]
+        y = (h[:, None] * y).T + self.ys[:, seg]
+        return y[:, 0] if t.ndim == 0 else y
+
+
+class IvpResult:
+    """t (n+1,), y (D, n+1), sol, status: the fields of scipy's solve_ivp result the reference reads (:124,135)."""
+
+    def __init__(self, t, y, sol, status):
+        self.t, self.y, self.sol, self.status = t, y, sol, status
+
+
+def _field_of(f):
+    vf_dict = getattr(f, "vf_dict", None)
+    if vf_dict is None:
+        raise NotImplementedError(
+            "integrate_vf_ivp on the B200 backend integrates this package's RKHS field (an object carrying vf_dict, "
+            "e.g. SvcVectorField.func / RkhsField); arbitrary Python callables have no device path and there is no "
+            "CPU fallback")
+    return vf_dict, float(getattr(f, "scale", 1.0))
+
+
+def solve_ivp_batch(init_states, vf_dict, t_span, max_step, scale=1.0, rtol=RTOL, atol=ATOL, cap=None):
+    """All initial states (n, D) from t_span[0] to t_span[1] on the device -> list of IvpResult, one per state,
+    equal to `solve_ivp(lambda t, x: scale * f(x), t_span, y0, events=<all |f| < 1e-5, terminal>, max_step=max_step,
+    dense_output=True)` of reference prediction/utils.py:115-135."""
+    Xc, beta, Cm = _vf_parts(vf_dict)
+    y0 = dev(np.ascontiguousarray(np.atleast_2d(np.asarray(init_states, dtype=np.float64))))
+    Xc, Cm = dev(Xc), dev(Cm)
+    n, D = y0.shape
+    M = Xc.shape[0]
+    if Xc.shape[1] != D:
+        raise ValueError("init_states must have the %d columns of X_ctrl, got %d" % (Xc.shape[1], D))
+    t0, tb = float(t_span[0]), float(t_span[1])
+    max_step = float(max_step)
+    if not max_step > 0:
+        raise ValueError("`max_step` must be positive.")      # scipy validate_max_step
+    span = abs(tb - t0)
+    if cap is None:
+        cap = int(min(max(span / max_step, 1.0), 1e6) * 1.25) + 64 if np.isfinite(max_step) else 1024
+    L = lib()
+    nbytes = C.c_size_t(0)
+    _lib.check(L.dvf_ivp_workspace_bytes(D, M, C.byref(nbytes)))
+    ws = torch.empty((nbytes.value + 7) // 8, dtype=torch.float64, device="cuda")
+    out = [None] * n
+    todo = np.arange(n)
+    while todo.size:
+        per = max(1, int(_BYTES_PER_LAUNCH // (8 * (cap + 1) * (5 * D + 1))))
+        again = []
+        for c0 in range(0, todo.size, per):
+            idx = todo[c0:c0 + per]
+            k = idx.size
+            ysel = y0[torch.as_tensor(idx, device=y0.device)].contiguous() if k != n else y0
+            ts = torch.empty((k, cap + 2), dtype=torch.float64, device="cuda")
+            ys = torch.empty((k, cap + 1, D), dtype=torch.float64, device="cuda")
+            Q = torch.empty((k, cap, D, 4), dtype=torch.float64, device="cuda")
+            ns = torch.empty((k,), dtype=torch.int32, device="cuda")
+            st = torch.empty((k,), dtype=torch.int32, device="cuda")
+            _lib.check(L.dvf_integrate_rk45(ptr(ysel), k, D, ptr(Xc), M, float(beta), ptr(Cm), float(scale), t0, tb,
+                                            max_step, float(rtol), float(atol), REST_TOL, cap, ptr(ts), ptr(ys),
+                                            ptr(Q), ptr(ns), ptr(st), ptr(ws), nbytes.value, stream_ptr()))
+            ns_h, st_h = ns.cpu().numpy(), st.cpu().numpy()
+            kmax = int(ns_h.max()) if k else 0
+            ts_h = ts[:, :kmax + 2].cpu().numpy()
+            ys_h = ys[:, :kmax + 1].cpu().numpy()
+            Q_h = Q[:, :max(kmax, 1)].cpu().numpy()
+            for j, i in enumerate(idx):
+                if st_h[j] == -2:
+                    again.append(i)
+                    continue
+                m = int(ns_h[j])
+                t_j = ts_h[j, :m + 1].copy()
+                y_j = np.ascontiguousarray(ys_h[j, :m + 1].T)
+                h_j = None
+                status = int(st_h[j])
+                if status == -3:
+                    # the event's root is the START of the first step (initial state and step end both at rest):
+                    # scipy returns t = [t0, t0], status 1, and an interpolant that keeps the step as taken
+                    h_j, status = np.array([ts_h[j, 2] - ts_h[j, 0]]), 1
+                out[i] = IvpResult(t_j, y_j, DenseSolution(t_j, y_j, Q_h[j, :m].copy(), h_j), status)
+        todo = np.asarray(again, dtype=np.int64)
+        cap *= 2
+    return out
+
+
+# ---- the reference's trajectory bookkeeping (host, O(steps x D) per trajectory) --------------------------------
+def _half_spectrum(col):
+    """vectorfield/topography.py:324-329 (calc_fft, amplitudes only)."""
+    n = len(col)
+    return (np.abs(np.fft.rfft(col)) / n * 2)[: int(n / 2)]
+
+
+def _repeat_cut(x, n_dom=3, tol=0.05):
+    """vectorfield/topography.py:332-368 (dup_osc_idx): compare the spectra of the last two thirds."""
+    L = int(np.floor(len(x) / n_dom))
+    a, b = x[(n_dom - 2) * L:(n_dom - 1) * L], x[(n_dom - 1) * L:n_dom * L]
+    try:
+        sa = np.hstack([_half_spectrum(a[:, k])[1:] for k in range(a.shape[1])])
+        sb = np.hstack([_half_spectrum(b[:, k])[1:] for k in range(b.shape[1])])
+    except ValueError:
+        return None, None
+    with np.errstate(invalid="ignore", divide="ignore"):
+        diff = np.linalg.norm(sa - sb) / len(sa)
+    return ((n_dom - 1) * L if diff <= tol else None), diff
+
+
+def _repeat_cut_iter(x, max_iter=5, **kw):
+    """vectorfield/topography.py:371-397 (dup_osc_idx_iter); returns the cut index only."""
+    idx, j = len(x), 0
+    while True:
+        i, _ = _repeat_cut(x[:idx], **kw)
+        if i is None:
+            break
+        idx = i
+        j += 1
+        if j >= max_iter or idx == 0:
+            break
+    return idx
+
+
+def _arclength_times(x, num, t):
+    """prediction/trajectory.py:568-592 (arclength_sampling_n), the resampled times only."""
+    arclen = np.hstack((0, np.cumsum(np.linalg.norm(np.diff(x, axis=0), axis=1))))
+    z = np.linspace(arclen[0], arclen[-1], num)
+    return interp1d(arclen, t)(z)
+
+
+def _eval_sol(sol, t, both):
+    if not both:
+        return sol(t)
+    neg = int(np.sum(np.asarray(t) < 0))
+    return np.hstack((sol[0](t[:neg]), sol[1](t[neg:])))
+
+
+def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interpolation_num=250, average=True,
+                     sampling="arc_length", verbose=False, disable=False):
+    """reference prediction/utils.py:62-259.  Returns (t, Y): lists with one time vector and one (D, n_points) array
+    per initial state."""
+    vf_dict, scale = _field_of(f)
+    init_states = np.asarray(init_states)
+    if init_states.ndim == 1:
+        init_states = init_states[None, :]
+    n_cell, n_feature = init_states.shape
+    t = np.asarray(t)
+    max_step = np.abs(t[-1] - t[0]) / interpolation_num                      # :96
+    if interpolation_num is not None and integration_direction == "both":
+        interpolation_num = interpolation_num * 2                             # :100-101
+    both = integration_direction == "both"
+    if integration_direction == "forward":
+        res = solve_ivp_batch(init_states, vf_dict, (t[0], t[-1]), max_step, scale)
+        T, Y, SOL = [r.t for r in res], [r.y for r in res], [r.sol for r in res]
+    elif integration_direction == "backward":
+        res = solve_ivp_batch(init_states, vf_dict, (-t[0], -t[-1]), max_step, scale)
+        T, Y, SOL = [r.t for r in res], [r.y for r in res], [r.sol for r in res]
+    elif both:
+        fw = solve_ivp_batch(init_states, vf_dict, (t[0], t[-1]), max_step, scale)
+        bw = solve_ivp_batch(init_states, vf_dict, (-t[0], -t[-1]), max_step, scale)
+        # :155-158 as written there: the backward STATES are flipped along the feature axis, the times along time
+        Y = [np.hstack((b.y[::-1, :], a.y)) for a, b in zip(fw, bw)]
+        T = [np.hstack((b.t[::-1], a.t)) for a, b in zip(fw, bw)]
+        SOL = [[b.sol, a.sol] for a, b in zip(fw, bw)]
+    else:
+        raise Exception("both, forward, backward are the only valid direction argument strings")
+
+    if sampling == "arc_length":                                             # :172-184, trajectory.py:141-176
+        t_out, Y_out = [], []
+        for i in range(n_cell):
+            tau, x = T[i], Y[i].T
+            idx = _repeat_cut_iter(x, max_iter=100, tol=(x.max(0) - x.min(0)).mean() / 1000)
+            ti = _arclength_times(x[:idx], interpolation_num + 1, tau[:idx])[1:]
+            t_out.append(ti)
+            Y_out.append(_eval_sol(SOL[i], ti, both))
+        return t_out, Y_out
+    if sampling == "logspace":                                               # :185-197, trajectory.py:178-224
+        t_out, Y_out = [], []
+        for i in range(n_cell):
+            tau = T[i]
+            neg_tau, pos_tau = tau[tau < 0], tau[tau >= 0]
+            if len(neg_tau) > 0:
+                t_0 = -(np.logspace(0, np.log10(abs(min(neg_tau)) + 1), interpolation_num)) - 1
+                t_1 = np.logspace(0, np.log10(max(pos_tau) + 1), interpolation_num) - 1
+                ti = np.hstack((t_0[::-1], t_1))
+            else:
+                ti = np.logspace(0, np.log10(max(tau) + 1), interpolation_num) - 1
+            t_out.append(ti)
+            Y_out.append(_eval_sol(SOL[i], ti, both))
+        return t_out, Y_out
+    if sampling == "uniform_indices":                                        # :198-257
+        t_uniq = np.unique(np.hstack(T))
+        if len(t_uniq) > interpolation_num:
+            valid_t = np.hstack([0, np.sort(t_uniq)])[(np.linspace(0, len(t_uniq), interpolation_num)).astype(int)]
+            if len(valid_t) != interpolation_num:
+                n_missed = interpolation_num - len(valid_t)
+                tmp = np.zeros(n_missed)
+                for i in range(n_missed):
+                    tmp[i] = (valid_t[i] + valid_t[i + 1]) / 2
+                valid_t = np.sort(np.hstack([tmp, valid_t]))
+        else:
+            valid_t = np.hstack((-np.linspace(min(t_uniq), 0, interpolation_num),
+                                 np.linspace(0, max(t_uniq), interpolation_num)))
+        Yall = np.hstack([_eval_sol(SOL[i], valid_t, both) for i in range(n_cell)])
+        tt = valid_t
+        if n_cell > 1 and average:
+            t_len = int(len(tt) / n_cell)
+            avg = np.zeros((n_feature, t_len))
+            for i in range(t_len):
+                avg[:, i] = np.mean(Yall[:, np.arange(n_cell) * t_len + i], 1)
+            Yall = avg
+        width = Yall.shape[1] // n_cell
+        return [tt] * n_cell, [Yall[:, i * width:(i + 1) * width] for i in range(n_cell)]
+    # the reference falls through with the raw solver output when `sampling` is none of the three
+    return t, Y

@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import importlib
 
-from . import svc, vf
+from . import integrate, svc, vf
 from .sparsevfc import SparseVFC
 
 _NAMES = {
@@ -30,11 +30,13 @@ _NAMES = {
     "compute_torsion": vf.compute_torsion,
     "compute_sensitivity": vf.compute_sensitivity,
     "vecfld_from_adata": svc.vecfld_from_adata,
+    "integrate_vf_ivp": integrate.integrate_vf_ivp,
     "SparseVFC": SparseVFC,
     "SvcVectorField": svc.SvcVectorField,
 }
 _MODULES = ("dynamo.vectorfield.utils", "dynamo.vectorfield.scVectorField", "dynamo.vectorfield.vector_calculus",
-            "dynamo.vectorfield.VectorField", "dynamo.vectorfield.rank_vf", "dynamo.vectorfield", "dynamo.vf")
+            "dynamo.vectorfield.VectorField", "dynamo.vectorfield.rank_vf", "dynamo.vectorfield", "dynamo.vf", "dynamo.prediction.utils",
+            "dynamo.prediction.fate")
 _saved = {}
 
 

@@ -32,6 +32,20 @@ def vecfld_from_adata(adata, basis="", vf_key="VecFld"):
     return vf_dict, _vf.RkhsField(vf_dict)
 
 
+def _t_end(X, V):
+    """tools/utils.py:3175-3189 (getTend): data extent over the 1st percentile of the non-zero speeds."""
+    V_abs = np.abs(V)
+    return np.max(X.max(0) - X.min(0)) / np.percentile(V_abs[V_abs > 0], 1)
+
+
+def _t_seq(init_states, t_end, step_size=None):
+    """tools/utils.py:3192-3209 (getTseq)."""
+    if step_size is None:
+        max_steps = int(max(7 / (init_states.shape[1] / 300), 4)) if init_states.shape[1] > 300 else 7
+        return np.linspace(0, t_end, 10 ** (np.min([int(np.log10(t_end)), max_steps])))
+    return np.arange(0, t_end + step_size, step_size)
+
+
 class SvcVectorField:
     """Same constructor, attributes (`data`, `vf_dict`, `func`, `parameters`, `norm_dict`, `normalize`) and
     methods as the reference class."""
@@ -78,6 +92,32 @@ class SvcVectorField:
 
     def get_data(self):
         return self.data["X"], self.data["V"]
+
+    # ---- BaseVectorField.integrate (:721-784) ----
+    def integrate(self, init_states, dims=None, scale=1, t_end=None, step_size=None, args=(),
+                  integration_direction="forward", interpolation_num=250, average=True, sampling="arc_length",
+                  verbose=False, disable=False):
+        """Integrate initial states through the field on the device (K11).  Like the reference, `scale` only takes
+        effect when `func` is still unset; `dims` must keep every dimension of the field (the kernel integrates the
+        full RKHS field)."""
+        from .integrate import ScaledRkhsField, integrate_vf_ivp
+
+        init_states = np.asarray(init_states)
+        if np.isscalar(dims):
+            init_states = init_states[:, :dims]
+        elif dims is not None:
+            init_states = init_states[:, dims]
+        if dims is not None and init_states.shape[1] != np.shape(self.vf_dict["X_ctrl"])[1]:
+            raise NotImplementedError("integrate(dims=...) over a subset of the field's dimensions is not served by "
+                                      "the B200 backend")
+        if self.func is None:
+            self.func = ScaledRkhsField(self.vf_dict, scale)
+        if t_end is None:
+            t_end = _t_end(self.get_X(), self.get_V())
+        return integrate_vf_ivp(init_states, t=_t_seq(init_states, t_end, step_size),
+                                integration_direction=integration_direction, f=self.func, args=args,
+                                interpolation_num=interpolation_num, average=average, sampling=sampling,
+                                verbose=verbose, disable=disable)
 
     # ---- train (:997-1046) ----
     def train(self, **kwargs):

@@ -121,6 +121,26 @@ int dvf_hessian(const double* x, int64_t n, int D, const double* Xc, int M, doub
 int dvf_laplacian(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
                   double* L, void* stream);
 
+/* ---- K11: batched initial-value integration through the field ------------------------------
+ * One adaptive Dormand-Prince 5(4) integration per initial state y0[i, :] of  y' = scale * f(y)  from t0 to t_bound,
+ * with the step control, the terminal "at rest" event all(|scale f| < rest_tol) and the dense-output coefficients of
+ * the scipy.integrate.solve_ivp call the reference makes per cell (prediction/utils.py:103-165, integrate_vf_ivp;
+ * event :107; max_step :96; right-hand side vectorfield/utils.py:73-142).  Per trajectory i (cap = step capacity):
+ *   ts[i, 0..k]      accepted times (k = n_steps[i] <= cap), ts row length cap + 2
+ *   ys[i, 0..k, :]   states at those times, (cap + 1) x D per trajectory
+ *   Q[i, s, :, 0..3] interpolant of step s:  y(t) = ys[s] + h (Q [x, x^2, x^3, x^4]),  x = (t - ts[s]) / h,
+ *                    h = ts[s+1] - ts[s]
+ *   status[i]        0 reached t_bound, 1 stopped by the event, -1 step size below 10 ulp(t) (scipy status -1),
+ *                    -2 more than cap steps (call again with a larger cap), -3 stopped by the event at the START of
+ *                    the first step (the initial state and the end of the first step are both at rest): k = 1,
+ *                    ts[i, 1] = t0, ys[i, 1] = y0, and ts[i, 2] holds the end of the step Q[i, 0] was built on
+ * workspace: dvf_ivp_workspace_bytes(D, M) (a transposed copy of Xc); M <= 5000. */
+int dvf_ivp_workspace_bytes(int D, int M, size_t* out);
+int dvf_integrate_rk45(const double* y0, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                       double scale, double t0, double t_bound, double max_step, double rtol, double atol,
+                       double rest_tol, int cap, double* ts, double* ys, double* Q, int* n_steps, int* status,
+                       void* ws, size_t ws_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * SparseVFC EM fit (vectorfield/scVectorField.py:417-497; Gaussian kernel branch)
  * ------------------------------------------------------------------------------------------- */

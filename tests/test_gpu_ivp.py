@@ -1,0 +1,118 @@
+"""GPU parity tests of K11 (batched initial-value integration), through the C ABI
+(dvf_integrate_rk45) and the reference-facing integrate_vf_ivp / SvcVectorField.integrate.
+
+The device integration must take the SAME accepted steps as scipy's solve_ivp does for the reference (same count,
+same status) and agree on times, states and the dense solution to <= 1e-9 of max|ref| (north_star: 1e-8): the only
+differences are summation order in the field evaluation (1e-16 per call) carried along the trajectory."""
+import numpy as np
+import pytest
+
+import ivp_util
+from golden_util import rel
+from oracle import ivp_oracle as io
+from oracle import vfc_oracle as vo
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+
+
+@pytest.fixture(scope="module")
+def it():
+    from dynamo_release_b200 import integrate
+
+    return integrate
+
+
+def test_raw_solver_output_matches_the_executed_reference(it):
+    z = ivp_util.load()
+    fr = z["sol_fractions"]
+    seen, worst = set(), 0.0
+    for name in ivp_util.FIELDS:
+        vf = ivp_util.field(z, name)
+        for te in z[f"{name}/t_end"]:
+            for sign, tag in ((1.0, "fw"), (-1.0, "bw")):
+                res = it.solve_ivp_batch(z[f"{name}/init"], vf, (sign * 0.0, sign * te), te / int(z["interp"]))
+                for i, r in enumerate(res):
+                    key = f"{name}/T{te:g}/raw_{tag}/{i}"
+                    assert r.status == int(z[key + "/status"]), key
+                    assert r.t.shape == z[key + "/t"].shape, key             # the same accepted steps
+                    tt = r.t[0] + fr * (r.t[-1] - r.t[0])
+                    e = max(rel(r.t, z[key + "/t"]), rel(r.y, z[key + "/y"]), rel(r.sol(tt), z[key + "/sol"]))
+                    worst = max(worst, e)
+                    assert e < TOL, (key, e)
+                    seen.add(r.status)
+    assert seen == {0, 1}
+    print("raw solver output vs reference: worst", worst)
+
+
+def test_integrate_vf_ivp_matches_the_executed_reference(it):
+    z = ivp_util.load()
+    interp = int(z["interp"])
+    worst = 0.0
+    for name, te, direction, sampling, average in ivp_util.combos(z):
+        f = it.RkhsField(ivp_util.field(z, name))
+        t, Y = it.integrate_vf_ivp(z[f"{name}/init"], np.linspace(0, te, 7), direction, f, interpolation_num=interp,
+                                   average=average, sampling=sampling, disable=True)
+        key = f"{name}/T{te:g}/{direction}/{sampling}/avg{int(average)}"
+        assert len(Y) == int(z[key + "/n"])
+        for i in range(len(Y)):
+            assert Y[i].shape == z[f"{key}/Y{i}"].shape
+            e = max(rel(t[i], z[f"{key}/t{i}"]), rel(Y[i], z[f"{key}/Y{i}"]))
+            worst = max(worst, e)
+            assert e < 1e-8, (key, i, e)
+    print("integrate_vf_ivp vs reference: worst", worst)
+
+
+@pytest.mark.parametrize("D,M,T,interp,scale", [(2, 20, 50.0, 250, 1.0), (30, 100, 3.0, 250, 1.0),
+                                                (50, 500, 2.0, 100, 0.5), (64, 257, 1.0, 60, 2.0),
+                                                (3, 25, 400.0, 4, 1.0), (1, 7, 5.0, 20, 1.0)])
+def test_batch_against_the_oracle(it, D, M, T, interp, scale):
+    """Random fields incl. loose max_step (rejected steps), D up to 64, ragged M, a scale factor."""
+    rng = np.random.default_rng(D * 1000 + M)
+    vf = {"X_ctrl": rng.normal(size=(M, D)), "C": rng.normal(size=(M, D)) * 0.3, "beta": 0.5 / D}
+    y0 = rng.normal(size=(12, D))
+    f = lambda x: scale * vo.field_eval(x, vf)  # noqa: E731
+    for sign in (1.0, -1.0):
+        res = it.solve_ivp_batch(y0, vf, (sign * 0.0, sign * T), T / interp, scale=scale)
+        for i in range(0, 12, 3):
+            g = io.rk45_solve(f, sign * 0.0, sign * T, y0[i], max_step=T / interp)
+            r = res[i]
+            assert r.status == g["status"] and r.t.shape == g["t"].shape
+            tt = np.linspace(r.t[0], r.t[-1], 33)
+            assert rel(r.t, g["t"]) < TOL and rel(r.y, g["y"]) < TOL
+            assert rel(r.sol(tt), io.dense_eval(g, tt)) < TOL
+
+
+def test_capacity_is_grown_and_groups_are_split(it, monkeypatch):
+    rng = np.random.default_rng(5)
+    vf = {"X_ctrl": rng.normal(size=(40, 4)), "C": rng.normal(size=(40, 4)) * 0.3, "beta": 0.2}
+    y0 = rng.normal(size=(37, 4))
+    full = it.solve_ivp_batch(y0, vf, (0.0, 6.0), 0.05)
+    monkeypatch.setattr(it, "_BYTES_PER_LAUNCH", 40000)       # a few trajectories per launch
+    small = it.solve_ivp_batch(y0, vf, (0.0, 6.0), 0.05, cap=8)  # 120+ steps needed: the capacity doubles
+    for a, b in zip(full, small):
+        assert np.array_equal(a.t, b.t) and np.array_equal(a.y, b.y) and a.status == b.status
+
+
+def test_start_at_rest_stops_at_once_like_scipy(it):
+    vf = {"X_ctrl": np.zeros((3, 2)), "C": np.zeros((3, 2)), "beta": 1.0}       # f == 0 everywhere
+    y0 = np.array([[1.0, 2.0], [-1.0, 0.5]])
+    for r, y in zip(it.solve_ivp_batch(y0, vf, (0.0, 1.0), 0.1), y0):
+        g = io.rk45_solve(lambda x: np.zeros(2), 0.0, 1.0, y, max_step=0.1)
+        assert r.status == g["status"] == 1
+        assert np.array_equal(r.t, g["t"]) and np.array_equal(r.t, [0.0, 0.0]) and np.array_equal(r.y, g["y"])
+        assert np.array_equal(r.sol(np.array([0.0, 5e-7])), np.stack([y, y], 1))
+
+
+def test_svc_integrate_method(it):
+    from dynamo_release_b200 import SvcVectorField
+
+    z = ivp_util.load()
+    vf = ivp_util.field(z, "sink")
+    X = z["sink/init"]
+    sv = SvcVectorField(vf_dict=dict(vf), func=None)
+    sv.data["X"], sv.data["V"] = X, it.RkhsField(vf)(X)
+    t, Y = sv.integrate(X, t_end=3.0, step_size=0.5, interpolation_num=40, sampling="logspace", disable=True)
+    key = "sink/T3/forward/logspace/avg1"
+    for i in range(len(Y)):
+        assert rel(Y[i], z[f"{key}/Y{i}"]) < 1e-8

@@ -1,0 +1,115 @@
+"""CPU tests of the trajectory-integration row: the oracle is pinned to scipy.integrate.solve_ivp
+(the third-party routine the reference calls, prediction/utils.py:115-135) and to golden vectors of the executed
+reference; the host-side sampling logic of dynamo_release_b200.integrate is checked against the same golden vectors
+with the oracle standing in for the device solver."""
+import numpy as np
+import pytest
+from scipy.integrate import solve_ivp
+
+import ivp_util
+from golden_util import rel
+from oracle import ivp_oracle as io
+from oracle import vfc_oracle as vo
+
+
+def _scipy_call(f, a, b, y0, max_step):
+    ev = lambda t, x: np.all(abs(f(x)) < 1e-5) - 1  # noqa: E731  (prediction/utils.py:107)
+    ev.terminal = True
+    return solve_ivp(lambda t, x: f(x), [a, b], y0, events=ev, max_step=max_step, dense_output=True)
+
+
+@pytest.mark.parametrize("D,M,T,interp", [(2, 20, 50.0, 250), (5, 40, 10.0, 100), (30, 100, 3.0, 250),
+                                          (3, 25, 400.0, 4), (4, 30, 30.0, 1)])
+def test_oracle_equals_scipy_solve_ivp_bit_for_bit(D, M, T, interp):
+    rng = np.random.default_rng(D * 1000 + M)
+    vf = {"X_ctrl": rng.normal(size=(M, D)), "C": rng.normal(size=(M, D)) * 0.3, "beta": 0.5 / D}
+    f = lambda x: vo.field_eval(x, vf)  # noqa: E731
+    statuses, steps = set(), set()
+    for k in range(3):
+        y0 = rng.normal(size=D)
+        for a, b in ((0.0, T), (-0.0, -T)):
+            r = _scipy_call(f, a, b, y0, T / interp)
+            g = io.rk45_solve(f, a, b, y0, max_step=T / interp)
+            assert r.status == g["status"]
+            assert np.array_equal(r.t, g["t"]) and np.array_equal(r.y, g["y"])
+            tt = np.linspace(a, r.t[-1], 41)
+            assert rel(io.dense_eval(g, tt), r.sol(tt)) < 1e-14    # scipy groups times per segment (GEMM vs dot)
+            statuses.add(r.status)
+            steps.add(len(r.t))
+    print("statuses", statuses, "steps", sorted(steps))
+
+
+def test_oracle_matches_reference_raw_solver_output():
+    z = ivp_util.load()
+    fr = z["sol_fractions"]
+    seen = set()
+    for name in ivp_util.FIELDS:
+        vf = ivp_util.field(z, name)
+        f = lambda x: vo.field_eval(x, vf)  # noqa: E731
+        for te in z[f"{name}/t_end"]:
+            for sign, tag in ((1.0, "fw"), (-1.0, "bw")):
+                for i, y0 in enumerate(z[f"{name}/init"]):
+                    key = f"{name}/T{te:g}/raw_{tag}/{i}"
+                    g = io.rk45_solve(f, sign * 0.0, sign * te, y0, max_step=te / int(z["interp"]))
+                    assert g["status"] == int(z[key + "/status"])
+                    assert g["t"].shape == z[key + "/t"].shape
+                    assert rel(g["t"], z[key + "/t"]) < 1e-12 and rel(g["y"], z[key + "/y"]) < 1e-12
+                    tt = g["t"][0] + fr * (g["t"][-1] - g["t"][0])
+                    assert rel(io.dense_eval(g, tt), z[key + "/sol"]) < 1e-12
+                    seen.add(g["status"])
+    assert seen == {0, 1}      # both "reached the end time" and "came to rest" are covered
+
+
+def test_host_sampling_logic_matches_reference(monkeypatch):
+    from dynamo_release_b200 import integrate as it
+
+    monkeypatch.setattr(it, "solve_ivp_batch", ivp_util.oracle_batch(it.DenseSolution, it.IvpResult))
+    z = ivp_util.load()
+    interp = int(z["interp"])
+    worst = 0.0
+    for name, te, direction, sampling, average in ivp_util.combos(z):
+        f = it.RkhsField(ivp_util.field(z, name))
+        t, Y = it.integrate_vf_ivp(z[f"{name}/init"], np.linspace(0, te, 7), direction, f, interpolation_num=interp,
+                                   average=average, sampling=sampling, disable=True)
+        key = f"{name}/T{te:g}/{direction}/{sampling}/avg{int(average)}"
+        assert len(Y) == int(z[key + "/n"])
+        for i in range(len(Y)):
+            assert Y[i].shape == z[f"{key}/Y{i}"].shape and np.shape(t[i]) == z[f"{key}/t{i}"].shape
+            e = max(rel(t[i], z[f"{key}/t{i}"]), rel(Y[i], z[f"{key}/Y{i}"]))
+            worst = max(worst, e)
+            assert e < 1e-10, (key, i, e)
+    print("worst relative difference to the reference:", worst)
+
+
+def test_dense_solution_equals_scipy_ode_solution():
+    from dynamo_release_b200.integrate import DenseSolution
+
+    rng = np.random.default_rng(3)
+    vf = {"X_ctrl": rng.normal(size=(30, 4)), "C": rng.normal(size=(30, 4)) * 0.4, "beta": 0.2}
+    f = lambda x: vo.field_eval(x, vf)  # noqa: E731
+    for a, b in ((0.0, 5.0), (-0.0, -5.0)):
+        r = _scipy_call(f, a, b, rng.normal(size=4), 0.1)
+        g = io.rk45_solve(f, a, b, r.y[:, 0], max_step=0.1)
+        s = DenseSolution(g["t"], g["y"], g["Q"], g["h"])
+        tt = np.concatenate([rng.uniform(min(a, b) - 0.5, max(a, b) + 0.5, 200), r.t])   # outside, inside, on the knots
+        assert rel(s(tt), r.sol(tt)) < 1e-14
+        assert rel(s(tt[7]), r.sol(tt[7])) < 1e-14 and s(tt[7]).shape == (4,)
+    with pytest.raises(ValueError):
+        DenseSolution(np.array([0.0, 0.0, 1.0]), np.zeros((4, 3)), np.zeros((2, 4, 4)))
+
+
+def test_start_at_rest_like_scipy():
+    """f == 0: the event's root is the start of the first step; scipy returns t = [0, 0], status 1."""
+    f = lambda x: np.zeros(2)  # noqa: E731
+    y0 = np.array([1.0, 2.0])
+    r = _scipy_call(f, 0.0, 1.0, y0, 0.1)
+    g = io.rk45_solve(f, 0.0, 1.0, y0, max_step=0.1)
+    assert r.status == g["status"] == 1 and np.array_equal(r.t, g["t"]) and np.array_equal(r.y, g["y"])
+    assert np.array_equal(r.sol(np.array([0.0, 5e-7])), io.dense_eval(g, np.array([0.0, 5e-7])))
+
+
+def test_generic_callable_is_refused():
+    from dynamo_release_b200.integrate import integrate_vf_ivp
+
+    with pytest.raises(NotImplementedError):
+        integrate_vf_ivp(np.zeros((1, 2)), np.linspace(0, 1, 3), "forward", lambda x: x)

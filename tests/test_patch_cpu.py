@@ -15,7 +15,7 @@ def ref_modules():
     ref_loader.install()
     mods = {m: ref_loader.load(m) for m in ("dynamo.vectorfield.utils", "dynamo.vectorfield.scVectorField",
                                             "dynamo.vectorfield.vector_calculus", "dynamo.vectorfield.VectorField",
-                                            "dynamo.vectorfield.rank_vf")}
+                                            "dynamo.vectorfield.rank_vf", "dynamo.prediction.utils")}
     return mods
 
 
@@ -29,7 +29,8 @@ def test_signatures_match_the_reference(ref_modules):
     from dynamo_release_b200 import patch
     utils, scvf = ref_modules["dynamo.vectorfield.utils"], ref_modules["dynamo.vectorfield.scVectorField"]
     for name, ours in patch._NAMES.items():
-        ref = getattr(utils, name, None) or getattr(scvf, name, None)
+        ref = getattr(utils, name, None) or getattr(scvf, name, None) or \
+            getattr(ref_modules["dynamo.prediction.utils"], name, None)
         assert ref is not None, name
         if inspect.isclass(ref):
             ref, ours = ref.__init__, ours.__init__
@@ -58,3 +59,9 @@ def test_install_rebinds_every_holder_and_uninstall_restores(ref_modules):
         patch.uninstall()
     for (m, n), fn in before.items():
         assert getattr(ref_modules[m], n) is fn
+
+
+def test_integrate_method_signature_matches_the_reference(ref_modules):
+    from dynamo_release_b200.svc import SvcVectorField
+    ref = ref_modules["dynamo.vectorfield.scVectorField"].SvcVectorField.integrate
+    assert _params(SvcVectorField.integrate) == _params(ref)
