@@ -59,6 +59,7 @@ SIGNATURES = {
     "dvf_ivp_workspace_bytes": (_i, [_i, _i, C.POINTER(_sz)]),
     "dvf_integrate_rk45": (_i, [_p, _i64, _i, _p, _i, _d, _p, _d, _d, _d, _d, _d, _d, _d, _i, _p, _p, _p, _p, _p,
                                 _p, _sz, _p]),
+    "dvf_ivp_dense_eval": (_i, [_p, _p, _p, _p, _p, _i, _i, _p, _p, _p, _i64, _i, _p, _p]),
     "dvf_fit_row_width": (_i64, [_i, _i]),
     "dvf_fit_workspace_bytes": (_i, [_i64, _i, _i, C.POINTER(_sz)]),
     "dvf_fit_em": (_i, [_p, _p, _i64, _i64, _i, _p, _i, _d, C.POINTER(EmParams), _p, _p, _p, _p, _p,

@@ -265,6 +265,44 @@ __global__ void k_ivp_transpose(const double* __restrict__ Xc, int M, int D, dou
     if (i < M * D) { const int m = i / D, d = i % D; XcT[(int64_t)d * M + m] = Xc[i]; }
 }
 
+// Dense-output evaluation of finished trajectories on the device (scipy OdeSolution.__call__ over RkDenseOutput pieces):
+// row r of t_eval belongs to trajectory traj[r]; the segment is chosen with numpy.searchsorted's rules (side "left" on
+// ascending times, "right" on the reversed array for descending ones, clipped to the first / last segment), then
+// y = ys[seg] + h (Q[seg] [x, x^2, x^3, x^4]).  One CTA per row; out is (m, D, S), sample index fastest.
+__global__ void __launch_bounds__(128) k_ivp_dense_eval(const double* __restrict__ ts, const double* __restrict__ ys,
+                                                        const double* __restrict__ Qs, const int* __restrict__ n_steps,
+                                                        const int* __restrict__ status, int D, int cap,
+                                                        const int* __restrict__ traj, const double* __restrict__ t_eval,
+                                                        const int* __restrict__ n_eval, int S, double* __restrict__ out) {
+    const int r = blockIdx.x;
+    const int64_t i = traj[r];
+    const int k = n_steps[i];
+    const int ne = n_eval ? n_eval[r] : S;
+    const double* t_i = ts + i * (int64_t)(cap + 2);
+    const double* y_i = ys + i * (int64_t)(cap + 1) * D;
+    const double* q_i = Qs + i * (int64_t)cap * D * 4;
+    const bool asc = t_i[k] >= t_i[0];
+    const bool at_start = status[i] == -3;
+    for (int e = threadIdx.x; e < ne * D; e += blockDim.x) {
+        const int j = e / D, d = e % D;
+        const double t = t_eval[(int64_t)r * S + j];
+        // cnt = #{ts < t} (ascending, side left)  or  #{ts <= t} (descending: side right on the reversed array)
+        int lo = 0, hi = k + 1;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            const double v = asc ? t_i[mid] : t_i[k - mid];
+            if (asc ? (v < t) : (v <= t)) lo = mid + 1; else hi = mid;
+        }
+        int seg = min(max(lo - 1, 0), k - 1);
+        if (!asc) seg = k - 1 - seg;
+        const double h = at_start ? (t_i[2] - t_i[0]) : (t_i[seg + 1] - t_i[seg]);
+        const double x = (t - t_i[seg]) / h;
+        const double p1 = x, p2 = p1 * x, p3 = p2 * x, p4 = p3 * x;
+        const double* q = q_i + ((int64_t)seg * D + d) * 4;
+        out[((int64_t)r * D + d) * S + j] = h * (((q[0] * p1 + q[1] * p2) + q[2] * p3) + q[3] * p4) + y_i[(int64_t)seg * D + d];
+    }
+}
+
 }  // namespace dvf
 
 using namespace dvf;
@@ -297,6 +335,19 @@ extern "C" int dvf_integrate_rk45(const double* y0, int64_t n, int D, const doub
     const size_t smem = (size_t)M * sizeof(double);
     k_ivp_rk45<<<(unsigned)n, IVP_THREADS, smem, st>>>(y0, n, D, XcT, M, beta, C, scale, t0, t_bound, max_step, rtol,
                                                        atol, rest_tol, cap, ts, ys, Q, n_steps, status);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}
+
+extern "C" int dvf_ivp_dense_eval(const double* ts, const double* ys, const double* Q, const int* n_steps,
+                                  const int* status, int D, int cap, const int* traj, const double* t_eval,
+                                  const int* n_eval, int64_t m, int S, double* out, void* stream) {
+    DVF_ARG(D >= 1 && D <= kMaxD && cap >= 1 && S >= 0 && m >= 0, "dvf_ivp_dense_eval: bad sizes");
+    if (m == 0 || S == 0) return DVF_OK;
+    DVF_ARG(ts && ys && Q && n_steps && status && traj && t_eval && out, "dvf_ivp_dense_eval: NULL pointer");
+    DVF_ARG(m <= 0x7fffffff, "dvf_ivp_dense_eval: at most 2^31 - 1 rows per call");
+    k_ivp_dense_eval<<<(unsigned)m, 128, 0, (cudaStream_t)stream>>>(ts, ys, Q, n_steps, status, D, cap, traj, t_eval,
+                                                                    n_eval, S, out);
     DVF_LAUNCH_CHECK();
     return DVF_OK;
 }

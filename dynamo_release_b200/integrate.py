@@ -19,11 +19,13 @@ import torch
 from scipy.interpolate import interp1d
 
 from . import _lib
-from .device import dev, lib, ptr, stream_ptr
+from .device import dev, host, lib, ptr, stream_ptr
 from .vf import RkhsField, _vf_parts
 
 RTOL, ATOL, REST_TOL = 1e-3, 1e-6, 1e-5     # solve_ivp defaults; event threshold of prediction/utils.py:107
 _BYTES_PER_LAUNCH = 1 << 30                 # trajectories are integrated in groups whose outputs fit this
+PROFILE = False                             # developer aid (tools/ivp_tune.py): CUDA-event time of the kernel launches
+KERNEL_MS = 0.0
 
 
 class ScaledRkhsField(RkhsField):
@@ -37,19 +39,36 @@ class ScaledRkhsField(RkhsField):
         return self.scale * super().__call__(x, **kw)
 
 
-class DenseSolution:
-    """The continuous solution of one trajectory: evaluates like scipy's OdeSolution over RkDenseOutput pieces
-    (scipy/integrate/_ivp/common.py, rk.py) but for all requested times at once."""
+class _DeviceBatch:
+    """What one dvf_integrate_rk45 launch left in HBM (times, states, interpolant coefficients of a group of
+    trajectories); kept alive by the solutions that refer to it so that they can be evaluated on the device."""
 
-    def __init__(self, ts, ys, Q, h=None):
+    def __init__(self, ts, ys, Q, ns, st, D, cap):
+        self.ts, self.ys, self.Q, self.ns, self.st, self.D, self.cap = ts, ys, Q, ns, st, D, cap
+
+
+class DenseSolution:
+    """The continuous solution of one trajectory.  Called with times it evaluates like scipy's OdeSolution over
+    RkDenseOutput pieces (scipy/integrate/_ivp/common.py, rk.py), for all requested times at once, in NumPy; solutions
+    produced by solve_ivp_batch keep their coefficients on the device (fetched only if this NumPy path is used) and
+    are evaluated there, many trajectories per launch, by dense_eval_many()."""
+
+    def __init__(self, ts, ys, Q=None, h=None, batch=None, slot=None):
         ts = np.asarray(ts)
         d = np.diff(ts)
         if not ((ts.size == 2 and ts[0] == ts[-1]) or np.all(d > 0) or np.all(d < 0)):
             raise ValueError("`ts` must be strictly increasing or decreasing.")
-        self.ts, self.ys, self.Q, self.h = ts, ys, Q, (d if h is None else np.asarray(h))
+        self.ts, self.ys, self._Q, self.h = ts, ys, Q, (d if h is None else np.asarray(h))
+        self.batch, self.slot = batch, slot
         self.n_segments = len(d)
         self.ascending = bool(ts[-1] >= ts[0])
         self.t_min, self.t_max = (ts[0], ts[-1]) if self.ascending else (ts[-1], ts[0])
+
+    @property
+    def Q(self):
+        if self._Q is None:
+            self._Q = self.batch.Q[self.slot, :self.n_segments].cpu().numpy()
+        return self._Q
 
     def __call__(self, t):
         t = np.asarray(t, dtype=np.float64)
@@ -68,6 +87,39 @@ class DenseSolution:
             + Qs[:, :, 3] * p[3][:, None]
         y = (h[:, None] * y).T + self.ys[:, seg]
         return y[:, 0] if t.ndim == 0 else y
+
+
+def dense_eval_many(sols, times):
+    """[sol(t) for sol, t in zip(sols, times)] -> list of (D, len(t)) arrays, with one dvf_ivp_dense_eval launch per
+    group of device-resident solutions (the interpolant coefficients never leave HBM)."""
+    out = [None] * len(sols)
+    groups = {}
+    for r, sol in enumerate(sols):
+        if sol.batch is None:
+            out[r] = sol(np.asarray(times[r], dtype=np.float64))        # built from host arrays by the caller
+        else:
+            groups.setdefault(id(sol.batch), (sol.batch, []))[1].append(r)
+    for batch, rows in groups.values():
+        m, D = len(rows), batch.D
+        ne = np.array([len(times[r]) for r in rows], dtype=np.int32)
+        S = int(ne.max())
+        if S == 0:
+            for r in rows:
+                out[r] = np.empty((D, 0))
+            continue
+        te = np.zeros((m, S))
+        for k, r in enumerate(rows):
+            te[k, :ne[k]] = times[r]
+        traj = np.array([sols[r].slot for r in rows], dtype=np.int32)
+        te_d, ne_d, traj_d = dev(te), dev(ne, torch.int32), dev(traj, torch.int32)
+        res = torch.empty((m, D, S), dtype=torch.float64, device="cuda")
+        _lib.check(lib().dvf_ivp_dense_eval(ptr(batch.ts), ptr(batch.ys), ptr(batch.Q), ptr(batch.ns), ptr(batch.st),
+                                            D, batch.cap, ptr(traj_d), ptr(te_d), ptr(ne_d), m, S, ptr(res),
+                                            stream_ptr()))
+        res_h = host(res)
+        for k, r in enumerate(rows):
+            out[r] = np.ascontiguousarray(res_h[k, :, :ne[k]])
+    return out
 
 
 class IvpResult:
@@ -123,14 +175,22 @@ def solve_ivp_batch(init_states, vf_dict, t_span, max_step, scale=1.0, rtol=RTOL
             Q = torch.empty((k, cap, D, 4), dtype=torch.float64, device="cuda")
             ns = torch.empty((k,), dtype=torch.int32, device="cuda")
             st = torch.empty((k,), dtype=torch.int32, device="cuda")
+            if PROFILE:
+                ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                ev0.record()
             _lib.check(L.dvf_integrate_rk45(ptr(ysel), k, D, ptr(Xc), M, float(beta), ptr(Cm), float(scale), t0, tb,
                                             max_step, float(rtol), float(atol), REST_TOL, cap, ptr(ts), ptr(ys),
                                             ptr(Q), ptr(ns), ptr(st), ptr(ws), nbytes.value, stream_ptr()))
+            if PROFILE:
+                global KERNEL_MS
+                ev1.record()
+                ev1.synchronize()
+                KERNEL_MS += ev0.elapsed_time(ev1)
             ns_h, st_h = ns.cpu().numpy(), st.cpu().numpy()
             kmax = int(ns_h.max()) if k else 0
-            ts_h = ts[:, :kmax + 2].cpu().numpy()
-            ys_h = ys[:, :kmax + 1].cpu().numpy()
-            Q_h = Q[:, :max(kmax, 1)].cpu().numpy()
+            ts_h = host(ts[:, :kmax + 2].contiguous())            # times and states go to the host (the reference's
+            ys_h = host(ys[:, :kmax + 1].contiguous())            # result fields); Q stays in HBM
+            batch = _DeviceBatch(ts, ys, Q, ns, st, D, cap)
             for j, i in enumerate(idx):
                 if st_h[j] == -2:
                     again.append(i)
@@ -144,7 +204,7 @@ def solve_ivp_batch(init_states, vf_dict, t_span, max_step, scale=1.0, rtol=RTOL
                     # the event's root is the START of the first step (initial state and step end both at rest):
                     # scipy returns t = [t0, t0], status 1, and an interpolant that keeps the step as taken
                     h_j, status = np.array([ts_h[j, 2] - ts_h[j, 0]]), 1
-                out[i] = IvpResult(t_j, y_j, DenseSolution(t_j, y_j, Q_h[j, :m].copy(), h_j), status)
+                out[i] = IvpResult(t_j, y_j, DenseSolution(t_j, y_j, None, h_j, batch=batch, slot=j), status)
         todo = np.asarray(again, dtype=np.int64)
         cap *= 2
     return out
@@ -192,11 +252,15 @@ def _arclength_times(x, num, t):
     return interp1d(arclen, t)(z)
 
 
-def _eval_sol(sol, t, both):
+def _eval_all(SOL, times, both):
+    """[SOL[i](times[i])] for every trajectory (prediction/trajectory.py:167-176, prediction/utils.py:231-242): for
+    "both" the negative times go to the backward solution and the rest to the forward one."""
     if not both:
-        return sol(t)
-    neg = int(np.sum(np.asarray(t) < 0))
-    return np.hstack((sol[0](t[:neg]), sol[1](t[neg:])))
+        return dense_eval_many(SOL, times)
+    neg = [int(np.sum(np.asarray(t) < 0)) for t in times]
+    back = dense_eval_many([s[0] for s in SOL], [t[:k] for t, k in zip(times, neg)])
+    fwd = dense_eval_many([s[1] for s in SOL], [t[k:] for t, k in zip(times, neg)])
+    return [np.hstack((b, f)) for b, f in zip(back, fwd)]
 
 
 def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interpolation_num=250, average=True,
@@ -230,16 +294,14 @@ def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interp
         raise Exception("both, forward, backward are the only valid direction argument strings")
 
     if sampling == "arc_length":                                             # :172-184, trajectory.py:141-176
-        t_out, Y_out = [], []
+        t_out = []
         for i in range(n_cell):
             tau, x = T[i], Y[i].T
             idx = _repeat_cut_iter(x, max_iter=100, tol=(x.max(0) - x.min(0)).mean() / 1000)
-            ti = _arclength_times(x[:idx], interpolation_num + 1, tau[:idx])[1:]
-            t_out.append(ti)
-            Y_out.append(_eval_sol(SOL[i], ti, both))
-        return t_out, Y_out
+            t_out.append(_arclength_times(x[:idx], interpolation_num + 1, tau[:idx])[1:])
+        return t_out, _eval_all(SOL, t_out, both)
     if sampling == "logspace":                                               # :185-197, trajectory.py:178-224
-        t_out, Y_out = [], []
+        t_out = []
         for i in range(n_cell):
             tau = T[i]
             neg_tau, pos_tau = tau[tau < 0], tau[tau >= 0]
@@ -250,8 +312,7 @@ def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interp
             else:
                 ti = np.logspace(0, np.log10(max(tau) + 1), interpolation_num) - 1
             t_out.append(ti)
-            Y_out.append(_eval_sol(SOL[i], ti, both))
-        return t_out, Y_out
+        return t_out, _eval_all(SOL, t_out, both)
     if sampling == "uniform_indices":                                        # :198-257
         t_uniq = np.unique(np.hstack(T))
         if len(t_uniq) > interpolation_num:
@@ -265,7 +326,7 @@ def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interp
         else:
             valid_t = np.hstack((-np.linspace(min(t_uniq), 0, interpolation_num),
                                  np.linspace(0, max(t_uniq), interpolation_num)))
-        Yall = np.hstack([_eval_sol(SOL[i], valid_t, both) for i in range(n_cell)])
+        Yall = np.hstack(_eval_all(SOL, [valid_t] * n_cell, both))
         tt = valid_t
         if n_cell > 1 and average:
             t_len = int(len(tt) / n_cell)

@@ -140,6 +140,14 @@ int dvf_integrate_rk45(const double* y0, int64_t n, int D, const double* Xc, int
                        double scale, double t0, double t_bound, double max_step, double rtol, double atol,
                        double rest_tol, int cap, double* ts, double* ys, double* Q, int* n_steps, int* status,
                        void* ws, size_t ws_bytes, void* stream);
+/* The continuous solution of trajectories integrated by dvf_integrate_rk45 (same ts / ys / Q / n_steps / status / cap),
+ * evaluated on the device: row r of t_eval (m x S, n_eval[r] <= S valid entries, NULL = all S) belongs to trajectory
+ * traj[r]; out (m, D, S) = what scipy's OdeSolution.__call__ returns for it (segment choice of numpy.searchsorted as in
+ * scipy/integrate/_ivp/common.py, clipped extrapolation from the first / last segment).  replaces `sol(self.t)` of
+ * prediction/trajectory.py:167-176,213-224 and `SOL[i](valid_t_trans)` of prediction/utils.py:231-242. */
+int dvf_ivp_dense_eval(const double* ts, const double* ys, const double* Q, const int* n_steps, const int* status,
+                       int D, int cap, const int* traj, const double* t_eval, const int* n_eval, int64_t m, int S,
+                       double* out, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * SparseVFC EM fit (vectorfield/scVectorField.py:417-497; Gaussian kernel branch)

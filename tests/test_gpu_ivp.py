@@ -104,6 +104,25 @@ def test_start_at_rest_stops_at_once_like_scipy(it):
         assert np.array_equal(r.sol(np.array([0.0, 5e-7])), np.stack([y, y], 1))
 
 
+def test_device_dense_evaluation_equals_numpy_path(it):
+    """dvf_ivp_dense_eval (coefficients stay in HBM) against the NumPy evaluation of the same solution, which the CPU
+    tests pin to scipy's OdeSolution: inside, outside (clipped extrapolation), exactly on the knots, ragged lengths."""
+    rng = np.random.default_rng(11)
+    vf = {"X_ctrl": rng.normal(size=(60, 5)), "C": rng.normal(size=(60, 5)) * 0.3, "beta": 0.1}
+    y0 = rng.normal(size=(9, 5))
+    for sign in (1.0, -1.0):
+        res = it.solve_ivp_batch(y0, vf, (sign * 0.0, sign * 4.0), 0.05)
+        times = []
+        for i, r in enumerate(res):
+            t = np.concatenate([rng.uniform(-5.0, 5.0, 17 * i), r.t[:: max(1, i)]])
+            times.append(t)
+        got = it.dense_eval_many([r.sol for r in res], times)
+        for r, t, g in zip(res, times, got):
+            assert g.shape == (5, len(t))
+            if len(t):
+                assert rel(g, r.sol(t)) < 1e-14
+
+
 def test_svc_integrate_method(it):
     from dynamo_release_b200 import SvcVectorField
 

@@ -15,15 +15,28 @@ rng = np.random.default_rng(0)
 vf = {"X_ctrl": rng.normal(size=(M, D)), "C": rng.normal(size=(M, D)) * 0.3, "beta": 0.5 / D}
 y0 = rng.normal(size=(n, D))
 T = 3.0
+it.PROFILE = True
 for rep in range(3):
+    it.KERNEL_MS = 0.0
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     res = it.solve_ivp_batch(y0, vf, (0.0, T), T / interp)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
 steps = sum(len(r.t) - 1 for r in res)
-print(f"K11 n={n} D={D} M={M} interp={interp}: {dt*1e3:.1f} ms incl. D2H and host objects, {n/dt:.0f} traj/s, "
-      f"{steps} accepted steps, ~{6*steps/dt/1e6:.2f} M field evaluations/s")
+print(f"K11 n={n} D={D} M={M} interp={interp}: kernel {it.KERNEL_MS:.1f} ms = {n/it.KERNEL_MS*1e3:.0f} traj/s, "
+      f"{6*steps/it.KERNEL_MS/1e3:.2f} M field evaluations/s, {6*steps*(5*M*D+M)/it.KERNEL_MS/1e9:.2f} TFLOP/s algorithmic; "
+      f"solve_ivp_batch {dt*1e3:.1f} ms (times / states to the host, result objects) = {n/dt:.0f} traj/s; "
+      f"{steps} accepted steps")
+f_dev = it.RkhsField(vf)
+for sampling in ("arc_length", "logspace"):
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    tt, Y = it.integrate_vf_ivp(y0, np.linspace(0, T, 7), "forward", f_dev, interpolation_num=interp, sampling=sampling,
+                                disable=True)
+    torch.cuda.synchronize()
+    de = time.perf_counter() - t0
+    print(f"  integrate_vf_ivp(sampling={sampling}): {de*1e3:.1f} ms = {n/de:.0f} traj/s")
 # kernel alone
 ts = time.perf_counter()
 f = lambda x: vo.field_eval(x, vf)  # noqa: E731
@@ -31,4 +44,4 @@ k = 8
 for i in range(k):
     io.rk45_solve(f, 0.0, T, y0[i], max_step=T / interp)
 dc = (time.perf_counter() - ts) / k
-print(f"oracle (NumPy, 1 thread): {dc*1e3:.1f} ms per trajectory = {1/dc:.1f} traj/s; ratio {n/dt*dc:.0f}x")
+print(f"oracle solve (NumPy, 1 thread): {dc*1e3:.1f} ms per trajectory = {1/dc:.1f} traj/s; solve_ivp_batch ratio {n/dt*dc:.0f}x")
