@@ -134,7 +134,9 @@ int dvf_laplacian(const double* x, int64_t n, int D, const double* Xc, int M, do
  *                    -2 more than cap steps (call again with a larger cap), -3 stopped by the event at the START of
  *                    the first step (the initial state and the end of the first step are both at rest): k = 1,
  *                    ts[i, 1] = t0, ys[i, 1] = y0, and ts[i, 2] holds the end of the step Q[i, 0] was built on
- * workspace: dvf_ivp_workspace_bytes(D, M) (a transposed copy of Xc); M <= 5000. */
+ * workspace: dvf_ivp_workspace_bytes(D, M) (a transposed copy of Xc and a padded copy of C; 16-byte aligned);
+ * M <= 5000.  A handful of initial states run one per CTA, larger batches four per CTA in lock step; both give the
+ * same trajectories (every sum is formed in the same order). */
 int dvf_ivp_workspace_bytes(int D, int M, size_t* out);
 int dvf_integrate_rk45(const double* y0, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
                        double scale, double t0, double t_bound, double max_step, double rtol, double atol,
