@@ -719,10 +719,12 @@ extern "C" int dvf_integrate_rk45(const double* y0, int64_t n, int D, const doub
     double* XcT = (double*)ws;
     k_ivp_transpose<<<(M * D + 255) / 256, 256, 0, st>>>(Xc, M, D, XcT);
     DVF_LAUNCH_CHECK();
-    // one trajectory per CTA for a handful of initial states, IVP_T per CTA otherwise (same results; DVF_IVP_VARIANT =
+    // one trajectory per CTA for a handful of initial states, IVP_T per CTA (built for 4 CTAs per SM: 59 ms against
+    // 72 ms with 3 and 163 ms with one trajectory per CTA for 4096 states, D = 30, M = 500) otherwise (same results;
+    // DVF_IVP_VARIANT =
     // 1 forces the former, 2 / 3 the latter compiled for 3 / 4 CTAs per SM: developer experiments and the test that
     // compares them)
-    int variant = (n >= 2 * IVP_T) ? 2 : 1;
+    int variant = (n >= 2 * IVP_T) ? 3 : 1;
     if (const char* e = getenv("DVF_IVP_VARIANT")) { const int v = atoi(e); if (v >= 1 && v <= 3) variant = v; }
     if (variant == 1) {
         const size_t smem = (size_t)M * sizeof(double);

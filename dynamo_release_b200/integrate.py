@@ -16,7 +16,6 @@ import ctypes as C
 
 import numpy as np
 import torch
-from scipy.interpolate import interp1d
 
 from . import _lib
 from .device import dev, host, lib, ptr, stream_ptr
@@ -161,10 +160,13 @@ def solve_ivp_batch(init_states, vf_dict, t_span, max_step, scale=1.0, rtol=RTOL
     nbytes = C.c_size_t(0)
     _lib.check(L.dvf_ivp_workspace_bytes(D, M, C.byref(nbytes)))
     ws = torch.empty((nbytes.value + 7) // 8, dtype=torch.float64, device="cuda")
+    wave = 16 * torch.cuda.get_device_properties(y0.device).multi_processor_count
     out = [None] * n
     todo = np.arange(n)
     while todo.size:
         per = max(1, int(_BYTES_PER_LAUNCH // (8 * (cap + 1) * (5 * D + 1))))
+        if per >= wave:
+            per -= per % wave                 # whole waves of the lock-step kernel (4 CTAs per SM x 4 trajectories)
         again = []
         for c0 in range(0, todo.size, per):
             idx = todo[c0:c0 + per]
@@ -196,8 +198,8 @@ def solve_ivp_batch(init_states, vf_dict, t_span, max_step, scale=1.0, rtol=RTOL
                     again.append(i)
                     continue
                 m = int(ns_h[j])
-                t_j = ts_h[j, :m + 1].copy()
-                y_j = np.ascontiguousarray(ys_h[j, :m + 1].T)
+                t_j = ts_h[j, :m + 1]            # views of the group's pinned host buffers
+                y_j = ys_h[j, :m + 1].T
                 h_j = None
                 status = int(st_h[j])
                 if status == -3:
@@ -211,45 +213,57 @@ def solve_ivp_batch(init_states, vf_dict, t_span, max_step, scale=1.0, rtol=RTOL
 
 
 # ---- the reference's trajectory bookkeeping (host, O(steps x D) per trajectory) --------------------------------
-def _half_spectrum(col):
-    """vectorfield/topography.py:324-329 (calc_fft, amplitudes only)."""
-    n = len(col)
-    return (np.abs(np.fft.rfft(col)) / n * 2)[: int(n / 2)]
+def _half_spectra(a):
+    """vectorfield/topography.py:324-329,349-354 (calc_fft per column: amplitudes without the mean term, columns
+    concatenated) for a stack of trajectories a (k, n, D) -> (k, D * (n // 2 - 1)): one transform along the time axis
+    for all trajectories and columns -- the same numbers as the reference's per-column calls."""
+    n = a.shape[1]
+    amp = (np.abs(np.fft.rfft(a, axis=1)) / n * 2)[:, : int(n / 2)][:, 1:]
+    return np.ascontiguousarray(amp.transpose(0, 2, 1)).reshape(len(a), -1)
 
 
-def _repeat_cut(x, n_dom=3, tol=0.05):
-    """vectorfield/topography.py:332-368 (dup_osc_idx): compare the spectra of the last two thirds."""
-    L = int(np.floor(len(x) / n_dom))
-    a, b = x[(n_dom - 2) * L:(n_dom - 1) * L], x[(n_dom - 1) * L:n_dom * L]
-    try:
-        sa = np.hstack([_half_spectrum(a[:, k])[1:] for k in range(a.shape[1])])
-        sb = np.hstack([_half_spectrum(b[:, k])[1:] for k in range(b.shape[1])])
-    except ValueError:
-        return None, None
-    with np.errstate(invalid="ignore", divide="ignore"):
-        diff = np.linalg.norm(sa - sb) / len(sa)
-    return ((n_dom - 1) * L if diff <= tol else None), diff
-
-
-def _repeat_cut_iter(x, max_iter=5, **kw):
-    """vectorfield/topography.py:371-397 (dup_osc_idx_iter); returns the cut index only."""
-    idx, j = len(x), 0
-    while True:
-        i, _ = _repeat_cut(x[:idx], **kw)
-        if i is None:
-            break
-        idx = i
-        j += 1
-        if j >= max_iter or idx == 0:
-            break
-    return idx
+def _repeat_cuts(xs, max_iter=5, n_dom=3):
+    """vectorfield/topography.py:332-397 (dup_osc_idx_iter over dup_osc_idx) for many trajectories: as long as the
+    spectra of the last two thirds of x[:idx] agree within tol, idx shrinks to the end of the second third.  The
+    sequence of candidate cuts depends on the length only, so trajectories of equal length go through the rounds
+    together (one batched FFT per round); tol as in prediction/trajectory.py:155."""
+    out = [len(x) for x in xs]
+    by_len = {}
+    for i, x in enumerate(xs):
+        by_len.setdefault(len(x), []).append(i)
+    for length, members in by_len.items():
+        act = np.array(members)
+        stack = np.stack([xs[i] for i in members])                          # (k, length, D)
+        tol = (stack.max(1) - stack.min(1)).mean(1) / 1000
+        idx, j = length, 0
+        while act.size:
+            L = int(np.floor(idx / n_dom))
+            try:
+                sa = _half_spectra(stack[:, (n_dom - 2) * L:(n_dom - 1) * L])
+                sb = _half_spectra(stack[:, (n_dom - 1) * L:n_dom * L])
+            except ValueError:          # empty thirds: the reference reports "calc_fft_k run failed" and stops
+                break
+            with np.errstate(invalid="ignore", divide="ignore"):
+                diff = np.array([np.linalg.norm(a - b) for a, b in zip(sa, sb)]) / sa.shape[1]
+            keep = diff <= tol
+            idx = (n_dom - 1) * L
+            act, stack, tol = act[keep], stack[keep], tol[keep]
+            for i in act:
+                out[i] = idx
+            j += 1
+            if j >= max_iter or idx == 0:
+                break
+    return out
 
 
 def _arclength_times(x, num, t):
-    """prediction/trajectory.py:568-592 (arclength_sampling_n), the resampled times only."""
+    """prediction/trajectory.py:568-592 (arclength_sampling_n), the resampled times only.  Its
+    interp1d(arclen, t)(z) is, for these 1-d float64 arrays, scipy's delegation to numpy.interp."""
     arclen = np.hstack((0, np.cumsum(np.linalg.norm(np.diff(x, axis=0), axis=1))))
+    if len(arclen) < 2:
+        raise ValueError("x and y arrays must have at least 2 entries")     # interp1d's own check
     z = np.linspace(arclen[0], arclen[-1], num)
-    return interp1d(arclen, t)(z)
+    return np.interp(z, arclen, t)
 
 
 def _eval_all(SOL, times, both):
@@ -294,11 +308,8 @@ def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interp
         raise Exception("both, forward, backward are the only valid direction argument strings")
 
     if sampling == "arc_length":                                             # :172-184, trajectory.py:141-176
-        t_out = []
-        for i in range(n_cell):
-            tau, x = T[i], Y[i].T
-            idx = _repeat_cut_iter(x, max_iter=100, tol=(x.max(0) - x.min(0)).mean() / 1000)
-            t_out.append(_arclength_times(x[:idx], interpolation_num + 1, tau[:idx])[1:])
+        cuts = _repeat_cuts([y.T for y in Y], max_iter=100)
+        t_out = [_arclength_times(Y[i].T[:cuts[i]], interpolation_num + 1, T[i][:cuts[i]])[1:] for i in range(n_cell)]
         return t_out, _eval_all(SOL, t_out, both)
     if sampling == "logspace":                                               # :185-197, trajectory.py:178-224
         t_out = []

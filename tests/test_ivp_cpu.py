@@ -113,3 +113,32 @@ def test_generic_callable_is_refused():
 
     with pytest.raises(NotImplementedError):
         integrate_vf_ivp(np.zeros((1, 2)), np.linspace(0, 1, 3), "forward", lambda x: x)
+
+
+def test_repeat_cut_equals_the_reference_on_periodic_trajectories():
+    """The batched restatement of dup_osc_idx_iter (vectorfield/topography.py:332-397) against the executed reference,
+    on limit-cycle-like curves where the cut really fires (several lengths, several periods, plus noise and a drift that
+    must NOT be cut).  Needs /root/reference (build container only)."""
+    from oracle import ref_loader
+
+    if not ref_loader.available():
+        pytest.skip("reference tree not present")
+    topo = ref_loader.load("dynamo.vectorfield.topography")
+    from dynamo_release_b200.integrate import _repeat_cuts
+
+    rng = np.random.default_rng(9)
+    xs = []
+    for n in (40, 251, 251, 252, 300, 3, 1):
+        for periods in (0.4, 3.0, 9.0, 27.0):
+            s = np.linspace(0, 2 * np.pi * periods, n)
+            x = np.stack([np.cos(s), np.sin(s), 0.3 * np.cos(2 * s)], 1) * rng.uniform(0.5, 2.0)
+            xs.append(x)
+            xs.append(x + 1e-3 * rng.normal(size=x.shape))
+            xs.append(x + np.linspace(0, 5, n)[:, None])
+    ours = _repeat_cuts(xs, max_iter=100)
+    fired = 0
+    for x, got in zip(xs, ours):
+        ref = topo.dup_osc_idx_iter(x, max_iter=100, tol=(x.max(0) - x.min(0)).mean() / 1000)[0]
+        assert got == ref
+        fired += ref != len(x)
+    assert fired >= 5
