@@ -449,6 +449,22 @@ __device__ __forceinline__ void ivp_field_t(const double* xin, double* fout, Ivp
     __syncthreads();
 }
 
+// out-of-line copy of the field evaluation: the caller's per-trajectory step state is saved around the call instead of
+// competing with the accumulators for registers inside the evaluation's loops
+template <bool PF>
+__device__ __noinline__ void ivp_field_t_call(const double* xin, double* fout, IvpSharedT& s, double* kv, int D, int Dp,
+                                              int M, const double* __restrict__ XcT, const double* __restrict__ Cp,
+                                              double beta, double scale) {
+    ivp_field_t<PF>(xin, fout, s, kv, D, Dp, M, XcT, Cp, beta, scale);
+}
+template <bool PF, bool NI>
+__device__ __forceinline__ void ivp_field_sel(const double* xin, double* fout, IvpSharedT& s, double* kv, int D, int Dp,
+                                              int M, const double* __restrict__ XcT, const double* __restrict__ Cp,
+                                              double beta, double scale) {
+    if (NI) ivp_field_t_call<PF>(xin, fout, s, kv, D, Dp, M, XcT, Cp, beta, scale);
+    else ivp_field_t<PF>(xin, fout, s, kv, D, Dp, M, XcT, Cp, beta, scale);
+}
+
 __device__ __forceinline__ void ivp_rms_t(const double* buf, int D, double (&out)[IVP_T]) {
     constexpr int T = IVP_T;
 #pragma unroll
@@ -472,7 +488,7 @@ __device__ __forceinline__ void ivp_at_rest_t(const double* f, int D, double tol
         for (int tr = 0; tr < T; ++tr) out[tr] = out[tr] && (fabs(f[d * T + tr]) < tol);
 }
 
-template <int MINB, bool PF>
+template <int MINB, bool PF, bool NI>
 __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* __restrict__ y0s, int64_t n, int D, int Dp,
                                                             const double* __restrict__ XcT, int M, double beta,
                                                             const double* __restrict__ Cp, double scale, double t0,
@@ -503,7 +519,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
     }
     if (tid < T && my_valid) ts_o[0] = t0;
     __syncthreads();
-    ivp_field_t<PF>(s.y, s.K[0], s, kv, D, Dp, M, XcT, Cp, beta, scale);
+    ivp_field_sel<PF, NI>(s.y, s.K[0], s, kv, D, Dp, M, XcT, Cp, beta, scale);
     bool rest_old[T];
     ivp_at_rest_t(s.K[0], D, rest_tol, rest_old);
 
@@ -526,7 +542,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
         const double my_h0 = ivp_pick(h0, my);
         for (int e = tid; e < E; e += IVP_THREADS) s.yt[e] = s.y[e] + (my_h0 * dir) * s.K[0][e];
         __syncthreads();
-        ivp_field_t<PF>(s.yt, s.K[1], s, kv, D, Dp, M, XcT, Cp, beta, scale);
+        ivp_field_sel<PF, NI>(s.yt, s.K[1], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         for (int e = tid; e < E; e += IVP_THREADS)
             s.buf[e] = (s.K[1][e] - s.K[0][e]) / (atol + fabs(s.y[e]) * rtol);
         __syncthreads();
@@ -591,7 +607,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
                 s.yt[e] = s.y[e] + dy * my_h;
             }
             __syncthreads();
-            ivp_field_t<PF>(s.yt, s.K[sg], s, kv, D, Dp, M, XcT, Cp, beta, scale);
+            ivp_field_sel<PF, NI>(s.yt, s.K[sg], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         }
         for (int e = tid; e < E; e += IVP_THREADS) {
             double dy = 0.0;
@@ -600,7 +616,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
             s.ynew[e] = s.y[e] + my_h * dy;
         }
         __syncthreads();
-        ivp_field_t<PF>(s.ynew, s.K[6], s, kv, D, Dp, M, XcT, Cp, beta, scale);
+        ivp_field_sel<PF, NI>(s.ynew, s.K[6], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         for (int e = tid; e < E; e += IVP_THREADS) {
             double er = 0.0;
 #pragma unroll
@@ -778,7 +794,7 @@ extern "C" int dvf_integrate_rk45(const double* y0, int64_t n, int D, const doub
     // 1 forces the former, 2 / 3 the latter compiled for 3 / 4 CTAs per SM: developer experiments and the test that
     // compares them)
     int variant = (n >= 2 * IVP_T) ? 3 : 1;
-    if (const char* e = getenv("DVF_IVP_VARIANT")) { const int v = atoi(e); if (v >= 1 && v <= 5) variant = v; }
+    if (const char* e = getenv("DVF_IVP_VARIANT")) { const int v = atoi(e); if (v >= 1 && v <= 6) variant = v; }
     if (variant == 1) {
         const size_t smem = (size_t)M * sizeof(double);
         k_ivp_rk45<<<(unsigned)n, IVP_THREADS, smem, st>>>(y0, n, D, XcT, M, beta, C, scale, t0, t_bound, max_step,
@@ -792,9 +808,11 @@ extern "C" int dvf_integrate_rk45(const double* y0, int64_t n, int D, const doub
     k_ivp_pad<<<(M * Dp + 255) / 256, 256, 0, st>>>(C, M, D, Dp, Cp);
     DVF_LAUNCH_CHECK();
     const size_t smem = (size_t)M * IVP_T * sizeof(double);
-    // 2 / 3: built for 3 / 4 CTAs per SM; 4 / 5: the same with register prefetch of the next operands
-    auto kern = (variant == 2) ? k_ivp_rk45_t<3, false> : (variant == 3) ? k_ivp_rk45_t<4, false>
-              : (variant == 4) ? k_ivp_rk45_t<3, true> : k_ivp_rk45_t<4, true>;
+    // 2 / 3: built for 3 / 4 CTAs per SM; 4: 3 with the field evaluation out of line; 5 / 6: 4 with register prefetch
+    // of the next operands, built for 4 / 3 CTAs per SM
+    auto kern = (variant == 2) ? k_ivp_rk45_t<3, false, false> : (variant == 3) ? k_ivp_rk45_t<4, false, false>
+              : (variant == 4) ? k_ivp_rk45_t<4, false, true> : (variant == 5) ? k_ivp_rk45_t<4, true, true>
+              : k_ivp_rk45_t<3, true, true>;
     if (smem + sizeof(IvpSharedT) > 48 * 1024)     // beyond the default limit: opt in (cheap, so not cached per device)
         DVF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ctas = (n + IVP_T - 1) / IVP_T;

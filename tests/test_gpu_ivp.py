@@ -93,12 +93,12 @@ def test_kernel_variants_return_the_same_trajectories(it, monkeypatch, D, M):
     vf = {"X_ctrl": rng.normal(size=(M, D)), "C": rng.normal(size=(M, D)) * 0.3, "beta": 0.5 / D}
     y0 = rng.normal(size=(11, D))
     outs = {}
-    for v in ("1", "2", "3", "4", "5"):
+    for v in ("1", "2", "3", "4", "5", "6"):
         monkeypatch.setenv("DVF_IVP_VARIANT", v)
         outs[v] = [it.solve_ivp_batch(y0, vf, (s * 0.0, s * 6.0), 6.0 / 20) for s in (1.0, -1.0)]
     monkeypatch.delenv("DVF_IVP_VARIANT")
     same = True
-    for v in ("2", "3", "4", "5"):
+    for v in ("2", "3", "4", "5", "6"):
         for ra, rb in zip(outs["1"], outs[v]):
             for a, b in zip(ra, rb):
                 assert a.status == b.status and a.t.shape == b.t.shape
