@@ -289,7 +289,7 @@ __device__ __forceinline__ X ivp_pick(const X (&a)[IVP_T], int i) {
 
 // rows [m0, m1) of k^T C for the column pair (2cp, 2cp+1) and the interleave classes c0 .. c0+NC-1 (class = (m - m0) mod 4;
 // the rows left over after the last full group of four belong to class 0)
-template <int NC, bool PF>
+template <int NC>
 __device__ __forceinline__ void ivp_phase2_t(const double* __restrict__ Cp, int Dp, const double* kv, int m0, int m1,
                                              int c0, int cp, double* out /* part[g] */) {
     constexpr int T = IVP_T;
@@ -299,26 +299,11 @@ __device__ __forceinline__ void ivp_phase2_t(const double* __restrict__ Cp, int 
 #pragma unroll
         for (int tr = 0; tr < T; ++tr) { acc[u][0][tr] = 0.0; acc[u][1][tr] = 0.0; }
     const int main_end = (m1 > m0) ? m0 + ((m1 - m0) / 4) * 4 : m0;
-    double2 cn[NC];      // PF: the coefficients of the next group of four rows are fetched while this one is used
-    if (PF && main_end > m0) {
-#pragma unroll
-        for (int u = 0; u < NC; ++u) cn[u] = *reinterpret_cast<const double2*>(Cp + (int64_t)(m0 + c0 + u) * Dp + 2 * cp);
-    }
     for (int m = m0; m < main_end; m += 4) {
-        double2 cc[NC];
-        if (PF) {
-#pragma unroll
-            for (int u = 0; u < NC; ++u) cc[u] = cn[u];
-            if (m + 4 < main_end) {
-#pragma unroll
-                for (int u = 0; u < NC; ++u)
-                    cn[u] = *reinterpret_cast<const double2*>(Cp + (int64_t)(m + 4 + c0 + u) * Dp + 2 * cp);
-            }
-        }
 #pragma unroll
         for (int u = 0; u < NC; ++u) {
             const int row = m + c0 + u;
-            const double2 c = PF ? cc[u] : *reinterpret_cast<const double2*>(Cp + (int64_t)row * Dp + 2 * cp);
+            const double2 c = *reinterpret_cast<const double2*>(Cp + (int64_t)row * Dp + 2 * cp);
             const double2 k01 = *reinterpret_cast<const double2*>(kv + row * T);
             const double2 k23 = *reinterpret_cast<const double2*>(kv + row * T + 2);
             const double k[T] = {k01.x, k01.y, k23.x, k23.y};
@@ -354,7 +339,6 @@ __device__ __forceinline__ void ivp_phase2_t(const double* __restrict__ Cp, int 
 }
 
 // f for the T states xin[d * T + tr] -> fout[d * T + tr]; xin visible on entry, fout visible on return
-template <bool PF>
 __device__ __forceinline__ void ivp_field_t(const double* xin, double* fout, IvpSharedT& s, double* kv, int D, int Dp,
                                             int M, const double* __restrict__ XcT, const double* __restrict__ Cp,
                                             double beta, double scale) {
@@ -365,43 +349,6 @@ __device__ __forceinline__ void ivp_field_t(const double* xin, double* fout, Ivp
         double da[T], db[T];
 #pragma unroll
         for (int tr = 0; tr < T; ++tr) { da[tr] = 0.0; db[tr] = 0.0; }
-        if (PF) {
-            // the coordinates of the next four dimensions are fetched while the current four are used (same sums)
-            constexpr int CH = 4;
-            double ca[CH], cb[CH], na[CH], nb[CH];
-#pragma unroll
-            for (int u = 0; u < CH; ++u) {
-                const int dd = min(u, D - 1);
-                ca[u] = XcT[(int64_t)dd * M + ma]; cb[u] = XcT[(int64_t)dd * M + mbb];
-                na[u] = 0.0; nb[u] = 0.0;
-            }
-            for (int d0 = 0; d0 < D; d0 += CH) {
-                if (d0 + CH < D) {
-#pragma unroll
-                    for (int u = 0; u < CH; ++u) {
-                        const int dd = min(d0 + CH + u, D - 1);
-                        na[u] = XcT[(int64_t)dd * M + ma]; nb[u] = XcT[(int64_t)dd * M + mbb];
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < CH; ++u) {
-                    const int d = d0 + u;
-                    if (d < D) {
-                        const double2 x01 = *reinterpret_cast<const double2*>(xin + d * T);
-                        const double2 x23 = *reinterpret_cast<const double2*>(xin + d * T + 2);
-                        const double xv[T] = {x01.x, x01.y, x23.x, x23.y};
-#pragma unroll
-                        for (int tr = 0; tr < T; ++tr) {
-                            const double ta = xv[tr] - ca[u], tb = xv[tr] - cb[u];
-                            da[tr] = fma(ta, ta, da[tr]);
-                            db[tr] = fma(tb, tb, db[tr]);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < CH; ++u) { ca[u] = na[u]; cb[u] = nb[u]; }
-            }
-        } else
         for (int d = 0; d < D; ++d) {
             const double ca = XcT[(int64_t)d * M + ma], cb = XcT[(int64_t)d * M + mbb];
             const double2 x01 = *reinterpret_cast<const double2*>(xin + d * T);
@@ -426,11 +373,11 @@ __device__ __forceinline__ void ivp_field_t(const double* xin, double* fout, Ivp
     if (D <= 32) {        // 16 column pairs x 8 groups: group g = quarter g / 2, classes {0, 1} or {2, 3}
         const int cp = tid & 15, g = tid >> 4, p = g >> 1;
         const int m0 = p * per, m1 = min(M, m0 + per);
-        if (2 * cp < Dp) ivp_phase2_t<2, PF>(Cp, Dp, kv, m0, m1, 2 * (g & 1), cp, s.part[g]);
+        if (2 * cp < Dp) ivp_phase2_t<2>(Cp, Dp, kv, m0, m1, 2 * (g & 1), cp, s.part[g]);
     } else {              // 32 column pairs x 4 groups: group = quarter, all four classes
         const int cp = tid & 31, g = tid >> 5;
         const int m0 = g * per, m1 = min(M, m0 + per);
-        if (2 * cp < Dp) ivp_phase2_t<4, PF>(Cp, Dp, kv, m0, m1, 0, cp, s.part[g]);
+        if (2 * cp < Dp) ivp_phase2_t<4>(Cp, Dp, kv, m0, m1, 0, cp, s.part[g]);
     }
     __syncthreads();
     for (int e = tid; e < D * T; e += IVP_THREADS) {
@@ -447,22 +394,6 @@ __device__ __forceinline__ void ivp_field_t(const double* xin, double* fout, Ivp
         fout[e] = scale * v;
     }
     __syncthreads();
-}
-
-// out-of-line copy of the field evaluation: the caller's per-trajectory step state is saved around the call instead of
-// competing with the accumulators for registers inside the evaluation's loops
-template <bool PF>
-__device__ __noinline__ void ivp_field_t_call(const double* xin, double* fout, IvpSharedT& s, double* kv, int D, int Dp,
-                                              int M, const double* __restrict__ XcT, const double* __restrict__ Cp,
-                                              double beta, double scale) {
-    ivp_field_t<PF>(xin, fout, s, kv, D, Dp, M, XcT, Cp, beta, scale);
-}
-template <bool PF, bool NI>
-__device__ __forceinline__ void ivp_field_sel(const double* xin, double* fout, IvpSharedT& s, double* kv, int D, int Dp,
-                                              int M, const double* __restrict__ XcT, const double* __restrict__ Cp,
-                                              double beta, double scale) {
-    if (NI) ivp_field_t_call<PF>(xin, fout, s, kv, D, Dp, M, XcT, Cp, beta, scale);
-    else ivp_field_t<PF>(xin, fout, s, kv, D, Dp, M, XcT, Cp, beta, scale);
 }
 
 __device__ __forceinline__ void ivp_rms_t(const double* buf, int D, double (&out)[IVP_T]) {
@@ -488,7 +419,7 @@ __device__ __forceinline__ void ivp_at_rest_t(const double* f, int D, double tol
         for (int tr = 0; tr < T; ++tr) out[tr] = out[tr] && (fabs(f[d * T + tr]) < tol);
 }
 
-template <int MINB, bool PF, bool NI>
+template <int MINB>
 __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* __restrict__ y0s, int64_t n, int D, int Dp,
                                                             const double* __restrict__ XcT, int M, double beta,
                                                             const double* __restrict__ Cp, double scale, double t0,
@@ -519,7 +450,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
     }
     if (tid < T && my_valid) ts_o[0] = t0;
     __syncthreads();
-    ivp_field_sel<PF, NI>(s.y, s.K[0], s, kv, D, Dp, M, XcT, Cp, beta, scale);
+    ivp_field_t(s.y, s.K[0], s, kv, D, Dp, M, XcT, Cp, beta, scale);
     bool rest_old[T];
     ivp_at_rest_t(s.K[0], D, rest_tol, rest_old);
 
@@ -542,7 +473,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
         const double my_h0 = ivp_pick(h0, my);
         for (int e = tid; e < E; e += IVP_THREADS) s.yt[e] = s.y[e] + (my_h0 * dir) * s.K[0][e];
         __syncthreads();
-        ivp_field_sel<PF, NI>(s.yt, s.K[1], s, kv, D, Dp, M, XcT, Cp, beta, scale);
+        ivp_field_t(s.yt, s.K[1], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         for (int e = tid; e < E; e += IVP_THREADS)
             s.buf[e] = (s.K[1][e] - s.K[0][e]) / (atol + fabs(s.y[e]) * rtol);
         __syncthreads();
@@ -607,7 +538,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
                 s.yt[e] = s.y[e] + dy * my_h;
             }
             __syncthreads();
-            ivp_field_sel<PF, NI>(s.yt, s.K[sg], s, kv, D, Dp, M, XcT, Cp, beta, scale);
+            ivp_field_t(s.yt, s.K[sg], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         }
         for (int e = tid; e < E; e += IVP_THREADS) {
             double dy = 0.0;
@@ -616,7 +547,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
             s.ynew[e] = s.y[e] + my_h * dy;
         }
         __syncthreads();
-        ivp_field_sel<PF, NI>(s.ynew, s.K[6], s, kv, D, Dp, M, XcT, Cp, beta, scale);
+        ivp_field_t(s.ynew, s.K[6], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         for (int e = tid; e < E; e += IVP_THREADS) {
             double er = 0.0;
 #pragma unroll
@@ -794,7 +725,7 @@ extern "C" int dvf_integrate_rk45(const double* y0, int64_t n, int D, const doub
     // 1 forces the former, 2 / 3 the latter compiled for 3 / 4 CTAs per SM: developer experiments and the test that
     // compares them)
     int variant = (n >= 2 * IVP_T) ? 3 : 1;
-    if (const char* e = getenv("DVF_IVP_VARIANT")) { const int v = atoi(e); if (v >= 1 && v <= 6) variant = v; }
+    if (const char* e = getenv("DVF_IVP_VARIANT")) { const int v = atoi(e); if (v >= 1 && v <= 3) variant = v; }
     if (variant == 1) {
         const size_t smem = (size_t)M * sizeof(double);
         k_ivp_rk45<<<(unsigned)n, IVP_THREADS, smem, st>>>(y0, n, D, XcT, M, beta, C, scale, t0, t_bound, max_step,
@@ -808,11 +739,7 @@ extern "C" int dvf_integrate_rk45(const double* y0, int64_t n, int D, const doub
     k_ivp_pad<<<(M * Dp + 255) / 256, 256, 0, st>>>(C, M, D, Dp, Cp);
     DVF_LAUNCH_CHECK();
     const size_t smem = (size_t)M * IVP_T * sizeof(double);
-    // 2 / 3: built for 3 / 4 CTAs per SM; 4: 3 with the field evaluation out of line; 5 / 6: 4 with register prefetch
-    // of the next operands, built for 4 / 3 CTAs per SM
-    auto kern = (variant == 2) ? k_ivp_rk45_t<3, false, false> : (variant == 3) ? k_ivp_rk45_t<4, false, false>
-              : (variant == 4) ? k_ivp_rk45_t<4, false, true> : (variant == 5) ? k_ivp_rk45_t<4, true, true>
-              : k_ivp_rk45_t<3, true, true>;
+    auto kern = (variant == 3) ? k_ivp_rk45_t<4> : k_ivp_rk45_t<3>;      // 128 / 168 registers: 4 / 3 CTAs per SM
     if (smem + sizeof(IvpSharedT) > 48 * 1024)     // beyond the default limit: opt in (cheap, so not cached per device)
         DVF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ctas = (n + IVP_T - 1) / IVP_T;

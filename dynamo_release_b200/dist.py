@@ -171,3 +171,24 @@ def fit_sharded(X_local, Y_local, M, comm: Comm, seed=0, beta=None, velocity_bas
                                                  velocity_based_sampling=velocity_based_sampling)
     st = fit_em(Xv, Yv, ctrl_t, beta, comm=comm.handle, N_total=n_total, **em)
     return st, ctrl_t, idx, beta, valid
+
+
+def integrate_sharded(init_states, t, integration_direction, f, dst=0, **kwargs):
+    """Trajectory integration over ranks ("replicas only": initial states are independent, there is
+    no exchange step).  Every rank integrates its contiguous slice of `init_states` with integrate_vf_ivp on its own
+    GPU; rank `dst` receives the lists of all ranks in the original order (other ranks get their own part back).
+    `sampling="uniform_indices"` shares one time grid between all trajectories (prediction/utils.py:198-257) and is
+    therefore not sharded."""
+    from .integrate import integrate_vf_ivp
+
+    if kwargs.get("sampling", "arc_length") == "uniform_indices":
+        raise NotImplementedError("uniform_indices couples all trajectories; integrate them on one rank")
+    world, rank = dist.get_world_size(), dist.get_rank()
+    init_states = np.atleast_2d(np.asarray(init_states))
+    lo, hi = shard_bounds(len(init_states), world, rank)
+    tt, Y = integrate_vf_ivp(init_states[lo:hi], t, integration_direction, f, **kwargs) if hi > lo else ([], [])
+    parts = [None] * world if rank == dst else None
+    dist.gather_object((tt, Y), parts, dst=dst)
+    if rank != dst:
+        return tt, Y
+    return [x for p in parts for x in p[0]], [y for p in parts for y in p[1]]

@@ -133,3 +133,42 @@ def test_sharded_prelude_equals_single_process(world):
     ret = mgr.dict()
     mp.spawn(_prelude_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
     assert dict(ret) == {r: "ok" for r in range(world)}
+
+
+def _ivp_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import ivp_util
+        from dynamo_release_b200 import integrate as it
+        from dynamo_release_b200.dist import integrate_sharded
+
+        # the NumPy oracle stands in for the device solver: this checks the sharding / gathering logic only
+        it.solve_ivp_batch = ivp_util.oracle_batch(it.DenseSolution, it.IvpResult)
+        z = ivp_util.load()
+        f = it.RkhsField(ivp_util.field(z, "sink"))
+        init = z["sink/init"]
+        t = np.linspace(0, 3.0, 7)
+        tt, Y = integrate_sharded(init, t, "forward", f, interpolation_num=int(z["interp"]), sampling="logspace",
+                                  disable=True)
+        if rank == 0:
+            key = "sink/T3/forward/logspace/avg1"
+            assert len(Y) == len(init)
+            for i in range(len(Y)):
+                assert np.allclose(Y[i], z[f"{key}/Y{i}"], rtol=0, atol=1e-10 * np.abs(z[f"{key}/Y{i}"]).max())
+                assert np.allclose(tt[i], z[f"{key}/t{i}"], rtol=1e-12)
+        else:
+            lo, hi = shard_bounds(len(init), world, rank)
+            assert len(Y) == hi - lo
+        with pytest.raises(NotImplementedError):
+            integrate_sharded(init, t, "forward", f, sampling="uniform_indices")
+        ret[rank] = True
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_trajectory_integration_gloo(world):
+    ret = mp.Manager().dict()
+    mp.spawn(_ivp_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
+    assert all(ret.get(r) for r in range(world))

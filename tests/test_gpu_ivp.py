@@ -85,20 +85,19 @@ def test_batch_against_the_oracle(it, D, M, T, interp, scale):
 
 @pytest.mark.parametrize("D,M", [(30, 500), (50, 203), (2, 20), (1, 7), (33, 64), (64, 129)])
 def test_kernel_variants_return_the_same_trajectories(it, monkeypatch, D, M):
-    """One trajectory per CTA (DVF_IVP_VARIANT=1) and four per CTA in lock step (2 / 3: compiled for 3 / 4 CTAs per SM; 4 / 5: the same with
-    register prefetch)
+    """One trajectory per CTA (DVF_IVP_VARIANT=1) and four per CTA in lock step (2 / 3: compiled for 3 / 4 CTAs per SM)
     form every sum in the same order: identical accepted steps; states compared to 1e-13 and reported if bit-identical.
     11 initial states: the last CTA of the lock-step kernel is ragged."""
     rng = np.random.default_rng(D + M)
     vf = {"X_ctrl": rng.normal(size=(M, D)), "C": rng.normal(size=(M, D)) * 0.3, "beta": 0.5 / D}
     y0 = rng.normal(size=(11, D))
     outs = {}
-    for v in ("1", "2", "3", "4", "5", "6"):
+    for v in ("1", "2", "3"):
         monkeypatch.setenv("DVF_IVP_VARIANT", v)
         outs[v] = [it.solve_ivp_batch(y0, vf, (s * 0.0, s * 6.0), 6.0 / 20) for s in (1.0, -1.0)]
     monkeypatch.delenv("DVF_IVP_VARIANT")
     same = True
-    for v in ("2", "3", "4", "5", "6"):
+    for v in ("2", "3"):
         for ra, rb in zip(outs["1"], outs[v]):
             for a, b in zip(ra, rb):
                 assert a.status == b.status and a.t.shape == b.t.shape
