@@ -9,7 +9,9 @@ Drop-in names (same signatures as dynamo.vectorfield.scVectorField / dynamo.vect
 """
 from .sparsevfc import SparseVFC, fit_em  # noqa: F401
 from .svc import SvcVectorField, vecfld_from_adata  # noqa: F401
-from .integrate import DenseSolution, ScaledRkhsField, integrate_vf_ivp, solve_ivp_batch  # noqa: F401
+from .integrate import (  # noqa: F401
+    DenseSolution, ScaledRkhsField, _fate, dense_eval_many, integrate_vf_ivp, solve_ivp_batch,
+)
 from .vf import (  # noqa: F401
     Hessian_rkhs_gaussian,
     Laplacian,

@@ -349,3 +349,27 @@ def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interp
         return [tt] * n_cell, [Yall[:, i * width:(i + 1) * width] for i in range(n_cell)]
     # the reference falls through with the raw solver output when `sampling` is none of the three
     return t, Y
+
+
+def _fate(VecFld, init_states, t_end=None, step_size=None, direction="both", interpolation_num=250, average=True,
+          sampling="arc_length", cores=1):
+    """reference prediction/fate.py:166-265: the time sequence of getTseq, integrate_vf_ivp, and -- for several cells
+    with `average` -- the mean state per sampled time point.  `cores` is accepted and ignored: the reference's thread
+    pool calls integrate_vf_ivp once per cell, which for these per-trajectory samplings gives what one batched launch
+    gives (it forces cores = 1 itself for "uniform_indices")."""
+    from .svc import _t_seq
+
+    init_states = np.asarray(init_states)
+    t, prediction = integrate_vf_ivp(init_states, _t_seq(init_states, t_end, step_size), direction, VecFld,
+                                     interpolation_num=interpolation_num, average=average, sampling=sampling)
+    if init_states.shape[0] > 1 and average:                                  # :246-262
+        t_stack, prediction_stack = np.hstack(t), np.hstack(prediction)
+        n_cell, n_feature = init_states.shape
+        if len(t_stack) > 0 and len(prediction_stack) > 0:
+            t_len = int(len(t_stack) / n_cell)
+            avg = np.zeros((n_feature, t_len))
+            for i in range(t_len):
+                avg[:, i] = np.mean(prediction_stack[:, np.arange(n_cell) * t_len + i], 1)
+            prediction = [avg]
+            t = [np.sort(np.unique(t))]
+    return t, prediction

@@ -31,6 +31,7 @@ _NAMES = {
     "compute_sensitivity": vf.compute_sensitivity,
     "vecfld_from_adata": svc.vecfld_from_adata,
     "integrate_vf_ivp": integrate.integrate_vf_ivp,
+    "_fate": integrate._fate,
     "SparseVFC": SparseVFC,
     "SvcVectorField": svc.SvcVectorField,
 }

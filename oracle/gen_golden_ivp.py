@@ -83,6 +83,19 @@ def main():
                     z[key + "/n"] = np.array(len(Y))
                     for i in range(len(Y)):
                         z[f"{key}/t{i}"], z[f"{key}/Y{i}"] = np.asarray(tt[i]), np.asarray(Y[i])
+        # prediction/fate.py:166-265 (_fate) on top of it: time sequence from getTseq, mean state per time point
+        # (the loader's bare `dynamo.vectorfield` package skips the heavy __init__, so the one name fate.py imports
+        # from it is bound by hand to the function that __init__ would have exported)
+        sys.modules["dynamo.vectorfield"].vector_field_function = vfu.vector_field_function
+        fate = ref_loader.load("dynamo.prediction.fate")
+        for direction in ("forward", "both"):
+            for sampling, average in (("arc_length", True), ("logspace", True), ("logspace", False)):
+                tt, Y = fate._fate(f, fd["init"], t_end=float(fd["t_end"][0]), step_size=0.5, direction=direction,
+                                   interpolation_num=INTERP, average=average, sampling=sampling)
+                key = f"{name}/fate/{direction}/{sampling}/avg{int(average)}"
+                z[key + "/n"] = np.array(len(Y))
+                for i in range(len(Y)):
+                    z[f"{key}/t{i}"], z[f"{key}/Y{i}"] = np.asarray(tt[i]), np.asarray(Y[i])
     path = os.path.join(OUT, "ivp_cases.npz")
     np.savez_compressed(path, **z)
     print("wrote", path, os.path.getsize(path), "bytes;", len(z), "arrays")

@@ -40,3 +40,28 @@ def oracle_batch(dense_cls, result_cls):
         return out
 
     return run
+
+
+FATE_CASES = [(d, s, a) for d in ("forward", "both") for s, a in (("arc_length", True), ("logspace", True),
+                                                                  ("logspace", False))]
+
+
+def check_fate(z, it, tol):
+    """_fate (prediction/fate.py:166-265) for every golden case; returns the worst relative difference."""
+    from golden_util import rel
+
+    worst = 0.0
+    for name in FIELDS:
+        f = it.RkhsField(field(z, name))
+        for direction, sampling, average in FATE_CASES:
+            t, Y = it._fate(f, z[f"{name}/init"], t_end=float(z[f"{name}/t_end"][0]), step_size=0.5,
+                            direction=direction, interpolation_num=int(z["interp"]), average=average,
+                            sampling=sampling)
+            key = f"{name}/fate/{direction}/{sampling}/avg{int(average)}"
+            assert len(Y) == int(z[key + "/n"]), key
+            for i in range(len(Y)):
+                assert Y[i].shape == z[f"{key}/Y{i}"].shape and np.shape(t[i]) == z[f"{key}/t{i}"].shape, key
+                e = max(rel(t[i], z[f"{key}/t{i}"]), rel(Y[i], z[f"{key}/Y{i}"]))
+                assert e < tol, (key, i, e)
+                worst = max(worst, e)
+    return worst

@@ -149,6 +149,10 @@ def test_device_dense_evaluation_equals_numpy_path(it):
                 assert rel(g, r.sol(t)) < 1e-14
 
 
+def test_fate_wrapper_matches_the_executed_reference(it):
+    print("_fate vs reference: worst", ivp_util.check_fate(ivp_util.load(), it, 1e-8))
+
+
 def test_svc_integrate_method(it):
     from dynamo_release_b200 import SvcVectorField
 

@@ -81,6 +81,13 @@ def test_host_sampling_logic_matches_reference(monkeypatch):
     print("worst relative difference to the reference:", worst)
 
 
+def test_fate_wrapper_matches_reference(monkeypatch):
+    from dynamo_release_b200 import integrate as it
+
+    monkeypatch.setattr(it, "solve_ivp_batch", ivp_util.oracle_batch(it.DenseSolution, it.IvpResult))
+    print("_fate vs reference: worst", ivp_util.check_fate(ivp_util.load(), it, 1e-10))
+
+
 def test_dense_solution_equals_scipy_ode_solution():
     from dynamo_release_b200.integrate import DenseSolution
 

@@ -16,6 +16,9 @@ def ref_modules():
     mods = {m: ref_loader.load(m) for m in ("dynamo.vectorfield.utils", "dynamo.vectorfield.scVectorField",
                                             "dynamo.vectorfield.vector_calculus", "dynamo.vectorfield.VectorField",
                                             "dynamo.vectorfield.rank_vf", "dynamo.prediction.utils")}
+    import sys
+    sys.modules["dynamo.vectorfield"].vector_field_function = mods["dynamo.vectorfield.utils"].vector_field_function
+    mods["dynamo.prediction.fate"] = ref_loader.load("dynamo.prediction.fate")
     return mods
 
 
@@ -30,7 +33,8 @@ def test_signatures_match_the_reference(ref_modules):
     utils, scvf = ref_modules["dynamo.vectorfield.utils"], ref_modules["dynamo.vectorfield.scVectorField"]
     for name, ours in patch._NAMES.items():
         ref = getattr(utils, name, None) or getattr(scvf, name, None) or \
-            getattr(ref_modules["dynamo.prediction.utils"], name, None)
+            getattr(ref_modules["dynamo.prediction.utils"], name, None) or \
+            getattr(ref_modules["dynamo.prediction.fate"], name, None)
         assert ref is not None, name
         if inspect.isclass(ref):
             ref, ours = ref.__init__, ours.__init__
