@@ -14,7 +14,10 @@ from __future__ import annotations
 
 import ctypes as C
 
+import os
+
 import numpy as np
+import scipy.fft
 import torch
 
 from . import _lib
@@ -25,6 +28,7 @@ RTOL, ATOL, REST_TOL = 1e-3, 1e-6, 1e-5     # solve_ivp defaults; event threshol
 _BYTES_PER_LAUNCH = 1 << 30                 # trajectories are integrated in groups whose outputs fit this
 PROFILE = False                             # developer aid (tools/ivp_tune.py): CUDA-event time of the kernel launches
 KERNEL_MS = 0.0
+_FFT_WORKERS = max(1, min(32, os.cpu_count() or 1))
 
 
 class ScaledRkhsField(RkhsField):
@@ -218,7 +222,8 @@ def _half_spectra(a):
     concatenated) for a stack of trajectories a (k, n, D) -> (k, D * (n // 2 - 1)): one transform along the time axis
     for all trajectories and columns -- the same numbers as the reference's per-column calls."""
     n = a.shape[1]
-    amp = (np.abs(np.fft.rfft(a, axis=1)) / n * 2)[:, : int(n / 2)][:, 1:]
+    # scipy.fft runs the same pocketfft transforms as numpy.fft (bit-identical, tests/test_ivp_cpu.py) on all host cores
+    amp = (np.abs(scipy.fft.rfft(a, axis=1, workers=_FFT_WORKERS)) / n * 2)[:, : int(n / 2)][:, 1:]
     return np.ascontiguousarray(amp.transpose(0, 2, 1)).reshape(len(a), -1)
 
 
@@ -227,7 +232,7 @@ def _repeat_cuts(xs, max_iter=5, n_dom=3):
     spectra of the last two thirds of x[:idx] agree within tol, idx shrinks to the end of the second third.  The
     sequence of candidate cuts depends on the length only, so trajectories of equal length go through the rounds
     together (one batched FFT per round); tol as in prediction/trajectory.py:155."""
-    out = [len(x) for x in xs]
+    out = np.array([len(x) for x in xs], dtype=np.int64)
     by_len = {}
     for i, x in enumerate(xs):
         by_len.setdefault(len(x), []).append(i)
@@ -244,12 +249,16 @@ def _repeat_cuts(xs, max_iter=5, n_dom=3):
             except ValueError:          # empty thirds: the reference reports "calc_fft_k run failed" and stops
                 break
             with np.errstate(invalid="ignore", divide="ignore"):
-                diff = np.array([np.linalg.norm(a - b) for a, b in zip(sa, sb)]) / sa.shape[1]
+                d = sa - sb
+                diff = np.sqrt(np.einsum("ij,ij->i", d, d)) / sa.shape[1]
+                # the reference's np.linalg.norm sums in BLAS order: decide with it wherever the two could differ
+                for r in np.flatnonzero(np.abs(diff - tol) <= 1e-9 * tol):
+                    diff[r] = np.linalg.norm(d[r]) / sa.shape[1]
             keep = diff <= tol
             idx = (n_dom - 1) * L
-            act, stack, tol = act[keep], stack[keep], tol[keep]
-            for i in act:
-                out[i] = idx
+            if not keep.all():
+                act, stack, tol = act[keep], stack[keep], tol[keep]
+            out[act] = idx
             j += 1
             if j >= max_iter or idx == 0:
                 break

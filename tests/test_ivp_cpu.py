@@ -149,3 +149,15 @@ def test_repeat_cut_equals_the_reference_on_periodic_trajectories():
         assert got == ref
         fired += ref != len(x)
     assert fired >= 5
+
+
+def test_threaded_scipy_fft_equals_numpy_fft_bitwise():
+    """The repeat cut uses scipy.fft.rfft(workers=...) where the reference calls numpy.fft.rfft per column."""
+    import scipy.fft
+
+    rng = np.random.default_rng(2)
+    a = rng.normal(size=(37, 251, 7))
+    for lo, hi in ((83, 166), (0, 1), (5, 7), (10, 13), (100, 200)):
+        got = scipy.fft.rfft(a[:, lo:hi], axis=1, workers=4)
+        ref = np.stack([[np.fft.rfft(a[i, lo:hi, k]) for k in range(7)] for i in range(37)]).transpose(0, 2, 1)
+        assert np.array_equal(got, ref)
