@@ -295,6 +295,8 @@ def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interp
     if init_states.ndim == 1:
         init_states = init_states[None, :]
     n_cell, n_feature = init_states.shape
+    if n_cell == 0:
+        return [], []                       # the reference's per-cell loops do not run
     t = np.asarray(t)
     max_step = np.abs(t[-1] - t[0]) / interpolation_num                      # :96
     if interpolation_num is not None and integration_direction == "both":

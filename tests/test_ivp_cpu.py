@@ -115,6 +115,13 @@ def test_start_at_rest_like_scipy():
     assert np.array_equal(r.sol(np.array([0.0, 5e-7])), io.dense_eval(g, np.array([0.0, 5e-7])))
 
 
+def test_no_initial_states_gives_empty_lists():
+    from dynamo_release_b200.integrate import RkhsField, integrate_vf_ivp
+
+    f = RkhsField({"X_ctrl": np.zeros((3, 2)), "C": np.zeros((3, 2)), "beta": 1.0})
+    assert integrate_vf_ivp(np.zeros((0, 2)), np.linspace(0, 1, 3), "forward", f) == ([], [])
+
+
 def test_generic_callable_is_refused():
     from dynamo_release_b200.integrate import integrate_vf_ivp
 
