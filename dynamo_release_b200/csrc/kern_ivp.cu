@@ -273,15 +273,11 @@ __global__ void __launch_bounds__(IVP_THREADS) k_ivp_rk45(const double* __restri
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int IVP_T = 4;
 
-// views into the CTA's dynamic shared memory, sized by the problem (ES = Dp * IVP_T doubles per vector) rather than by
-// the largest supported D: at D = 30, M = 500 a CTA holds 34 KB instead of 55 KB, which leaves L1 room for Xc^T and C
-struct IvpSharedT {
-    double *y, *yt, *ynew, *buf, *K0, *part0;
-    int ES;
-    __device__ __forceinline__ double* K(int j) const { return K0 + j * ES; }
-    __device__ __forceinline__ double* part(int g) const { return part0 + g * ES; }
+struct __align__(16) IvpSharedT {
+    double y[kMaxD * IVP_T], yt[kMaxD * IVP_T], ynew[kMaxD * IVP_T], buf[kMaxD * IVP_T];
+    double K[7][kMaxD * IVP_T];
+    double part[8][kMaxD * IVP_T];
 };
-constexpr int IVP_VECS = 4 + 7 + 8;      // y, yt, ynew, buf, seven stages, eight partial-sum rows
 
 template <typename X>
 __device__ __forceinline__ X ivp_pick(const X (&a)[IVP_T], int i) {
@@ -343,7 +339,7 @@ __device__ __forceinline__ void ivp_phase2_t(const double* __restrict__ Cp, int 
 }
 
 // f for the T states xin[d * T + tr] -> fout[d * T + tr]; xin visible on entry, fout visible on return
-__device__ __forceinline__ void ivp_field_t(const double* xin, double* fout, const IvpSharedT& s, double* kv, int D, int Dp,
+__device__ __forceinline__ void ivp_field_t(const double* xin, double* fout, IvpSharedT& s, double* kv, int D, int Dp,
                                             int M, const double* __restrict__ XcT, const double* __restrict__ Cp,
                                             double beta, double scale) {
     constexpr int T = IVP_T;
@@ -377,23 +373,23 @@ __device__ __forceinline__ void ivp_field_t(const double* xin, double* fout, con
     if (D <= 32) {        // 16 column pairs x 8 groups: group g = quarter g / 2, classes {0, 1} or {2, 3}
         const int cp = tid & 15, g = tid >> 4, p = g >> 1;
         const int m0 = p * per, m1 = min(M, m0 + per);
-        if (2 * cp < Dp) ivp_phase2_t<2>(Cp, Dp, kv, m0, m1, 2 * (g & 1), cp, s.part(g));
+        if (2 * cp < Dp) ivp_phase2_t<2>(Cp, Dp, kv, m0, m1, 2 * (g & 1), cp, s.part[g]);
     } else {              // 32 column pairs x 4 groups: group = quarter, all four classes
         const int cp = tid & 31, g = tid >> 5;
         const int m0 = g * per, m1 = min(M, m0 + per);
-        if (2 * cp < Dp) ivp_phase2_t<4>(Cp, Dp, kv, m0, m1, 0, cp, s.part(g));
+        if (2 * cp < Dp) ivp_phase2_t<4>(Cp, Dp, kv, m0, m1, 0, cp, s.part[g]);
     }
     __syncthreads();
     for (int e = tid; e < D * T; e += IVP_THREADS) {
         double v;
         if (D <= 32) {
-            v = s.part(0)[e] + s.part(1)[e];
+            v = s.part[0][e] + s.part[1][e];
 #pragma unroll
-            for (int q = 1; q < IVP_PARTS; ++q) v += s.part(2 * q)[e] + s.part(2 * q + 1)[e];
+            for (int q = 1; q < IVP_PARTS; ++q) v += s.part[2 * q][e] + s.part[2 * q + 1][e];
         } else {
-            v = s.part(0)[e];
+            v = s.part[0][e];
 #pragma unroll
-            for (int q = 1; q < IVP_PARTS; ++q) v += s.part(q)[e];
+            for (int q = 1; q < IVP_PARTS; ++q) v += s.part[q][e];
         }
         fout[e] = scale * v;
     }
@@ -432,12 +428,8 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
                                                             double* __restrict__ ys, double* __restrict__ Qs,
                                                             int* __restrict__ n_steps, int* __restrict__ status) {
     constexpr int T = IVP_T;
-    extern __shared__ __align__(16) double kv[];      // M x T kernel values, then the state vectors
-    IvpSharedT s;
-    s.ES = Dp * T;
-    s.y = kv + (size_t)M * T;
-    s.yt = s.y + s.ES; s.ynew = s.yt + s.ES; s.buf = s.ynew + s.ES;
-    s.K0 = s.buf + s.ES; s.part0 = s.K0 + 7 * s.ES;
+    extern __shared__ __align__(16) double kv[];      // M x T kernel values
+    __shared__ IvpSharedT s;
     const int tid = threadIdx.x;
     const int my = tid & (T - 1);                      // every element this thread owns belongs to trajectory slot `my`
     const int64_t base = (int64_t)blockIdx.x * T;
@@ -458,9 +450,9 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
     }
     if (tid < T && my_valid) ts_o[0] = t0;
     __syncthreads();
-    ivp_field_t(s.y, s.K(0), s, kv, D, Dp, M, XcT, Cp, beta, scale);
+    ivp_field_t(s.y, s.K[0], s, kv, D, Dp, M, XcT, Cp, beta, scale);
     bool rest_old[T];
-    ivp_at_rest_t(s.K(0), D, rest_tol, rest_old);
+    ivp_at_rest_t(s.K[0], D, rest_tol, rest_old);
 
     const double span = fabs(t_bound - t0);
     double h_abs[T];
@@ -470,7 +462,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
         __syncthreads();
         ivp_rms_t(s.buf, D, d0);
         __syncthreads();
-        for (int e = tid; e < E; e += IVP_THREADS) s.buf[e] = s.K(0)[e] / (atol + fabs(s.y[e]) * rtol);
+        for (int e = tid; e < E; e += IVP_THREADS) s.buf[e] = s.K[0][e] / (atol + fabs(s.y[e]) * rtol);
         __syncthreads();
         ivp_rms_t(s.buf, D, d1);
 #pragma unroll
@@ -479,11 +471,11 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
             h0[tr] = fmin(h0[tr], span);
         }
         const double my_h0 = ivp_pick(h0, my);
-        for (int e = tid; e < E; e += IVP_THREADS) s.yt[e] = s.y[e] + (my_h0 * dir) * s.K(0)[e];
+        for (int e = tid; e < E; e += IVP_THREADS) s.yt[e] = s.y[e] + (my_h0 * dir) * s.K[0][e];
         __syncthreads();
-        ivp_field_t(s.yt, s.K(1), s, kv, D, Dp, M, XcT, Cp, beta, scale);
+        ivp_field_t(s.yt, s.K[1], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         for (int e = tid; e < E; e += IVP_THREADS)
-            s.buf[e] = (s.K(1)[e] - s.K(0)[e]) / (atol + fabs(s.y[e]) * rtol);
+            s.buf[e] = (s.K[1][e] - s.K[0][e]) / (atol + fabs(s.y[e]) * rtol);
         __syncthreads();
         ivp_rms_t(s.buf, D, d2);
 #pragma unroll
@@ -542,24 +534,24 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
         for (int sg = 1; sg < 6; ++sg) {
             for (int e = tid; e < E; e += IVP_THREADS) {
                 double dy = 0.0;
-                for (int j = 0; j < sg; ++j) dy += s.K(j)[e] * c_A[sg][j];
+                for (int j = 0; j < sg; ++j) dy += s.K[j][e] * c_A[sg][j];
                 s.yt[e] = s.y[e] + dy * my_h;
             }
             __syncthreads();
-            ivp_field_t(s.yt, s.K(sg), s, kv, D, Dp, M, XcT, Cp, beta, scale);
+            ivp_field_t(s.yt, s.K[sg], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         }
         for (int e = tid; e < E; e += IVP_THREADS) {
             double dy = 0.0;
 #pragma unroll
-            for (int j = 0; j < 6; ++j) dy += s.K(j)[e] * c_B[j];
+            for (int j = 0; j < 6; ++j) dy += s.K[j][e] * c_B[j];
             s.ynew[e] = s.y[e] + my_h * dy;
         }
         __syncthreads();
-        ivp_field_t(s.ynew, s.K(6), s, kv, D, Dp, M, XcT, Cp, beta, scale);
+        ivp_field_t(s.ynew, s.K[6], s, kv, D, Dp, M, XcT, Cp, beta, scale);
         for (int e = tid; e < E; e += IVP_THREADS) {
             double er = 0.0;
 #pragma unroll
-            for (int j = 0; j < 7; ++j) er += s.K(j)[e] * c_E[j];
+            for (int j = 0; j < 7; ++j) er += s.K[j][e] * c_E[j];
             const double sc = atol + fmax(fabs(s.y[e]), fabs(s.ynew[e])) * rtol;
             s.buf[e] = er * my_h / sc;
         }
@@ -567,7 +559,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
         double err[T];
         ivp_rms_t(s.buf, D, err);
         bool rest_new[T];
-        ivp_at_rest_t(s.K(6), D, rest_tol, rest_new);
+        ivp_at_rest_t(s.K[6], D, rest_tol, rest_new);
 
         // ---- decisions (identical in every thread) ----
         bool accept[T], stop[T];
@@ -604,7 +596,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
                 double q[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
                 for (int j = 0; j < 7; ++j) {
-                    const double k = s.K(j)[e];
+                    const double k = s.K[j][e];
 #pragma unroll
                     for (int c = 0; c < 4; ++c) q[c] += k * c_P[j][c];
                 }
@@ -624,7 +616,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
             for (int e = tid; e < E; e += IVP_THREADS) {
                 const double v = s.ynew[e];
                 s.y[e] = v;
-                s.K(0)[e] = s.K(6)[e];
+                s.K[0][e] = s.K[6][e];
                 if (my_valid) ys_o[(int64_t)(my_nst + 1) * D + e / T] = v;
             }
             if (tid < T && my_valid) {
@@ -746,9 +738,9 @@ extern "C" int dvf_integrate_rk45(const double* y0, int64_t n, int D, const doub
     DVF_ARG((((uintptr_t)Cp) & 15) == 0, "dvf_integrate_rk45: workspace must be 16-byte aligned");
     k_ivp_pad<<<(M * Dp + 255) / 256, 256, 0, st>>>(C, M, D, Dp, Cp);
     DVF_LAUNCH_CHECK();
-    const size_t smem = ((size_t)M * IVP_T + (size_t)IVP_VECS * Dp * IVP_T) * sizeof(double);
+    const size_t smem = (size_t)M * IVP_T * sizeof(double);
     auto kern = (variant == 3) ? k_ivp_rk45_t<4> : k_ivp_rk45_t<3>;      // 128 / 168 registers: 4 / 3 CTAs per SM
-    if (smem > 48 * 1024)     // beyond the default limit: opt in (cheap, so not cached per device)
+    if (smem + sizeof(IvpSharedT) > 48 * 1024)     // beyond the default limit: opt in (cheap, so not cached per device)
         DVF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ctas = (n + IVP_T - 1) / IVP_T;
     kern<<<(unsigned)ctas, IVP_THREADS, smem, st>>>(y0, n, D, Dp, XcT, M, beta, Cp, scale, t0, t_bound, max_step, rtol,
