@@ -286,6 +286,23 @@ def _eval_all(SOL, times, both):
     return [np.hstack((b, f)) for b, f in zip(back, fwd)]
 
 
+RESIDENT_BYTES = None      # HBM budget for the dense solutions of one slice of cells; None = half of the free memory
+
+
+def _resident_budget():
+    if RESIDENT_BYTES is not None:
+        return RESIDENT_BYTES
+    if torch.cuda.is_available():
+        return torch.cuda.mem_get_info()[0] // 2
+    return 1 << 34
+
+
+def _resident_bytes_per_cell(t, interpolation_num, D):
+    """What solve_ivp_batch keeps on the device per trajectory (its step capacity x times, states, coefficients)."""
+    cap = int(min(max(float(interpolation_num), 1.0), 1e6) * 1.25) + 64
+    return 8 * (cap + 2) * (5 * D + 1)
+
+
 def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interpolation_num=250, average=True,
                      sampling="arc_length", verbose=False, disable=False):
     """reference prediction/utils.py:62-259.  Returns (t, Y): lists with one time vector and one (D, n_points) array
@@ -298,6 +315,21 @@ def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interp
     if n_cell == 0:
         return [], []                       # the reference's per-cell loops do not run
     t = np.asarray(t)
+    if integration_direction not in ("forward", "backward", "both"):
+        raise Exception("both, forward, backward are the only valid direction argument strings")
+    # The dense solutions stay in HBM until they have been resampled.  arc_length / logspace treat every trajectory on
+    # its own, so a large set of cells goes through solve -> resample -> evaluate in slices that fit the memory budget
+    # (uniform_indices shares one time grid between all trajectories and needs them all at once).
+    per_cell = _resident_bytes_per_cell(t, interpolation_num, n_feature) * (2 if integration_direction == "both" else 1)
+    slice_cells = max(1, int(_resident_budget() // per_cell))
+    if sampling in ("arc_length", "logspace") and n_cell > slice_cells:
+        tt, YY = [], []
+        for c0 in range(0, n_cell, slice_cells):
+            a, b = integrate_vf_ivp(init_states[c0:c0 + slice_cells], t, integration_direction, f, args,
+                                    interpolation_num, average, sampling, verbose, disable)
+            tt += a
+            YY += b
+        return tt, YY
     max_step = np.abs(t[-1] - t[0]) / interpolation_num                      # :96
     if interpolation_num is not None and integration_direction == "both":
         interpolation_num = interpolation_num * 2                             # :100-101

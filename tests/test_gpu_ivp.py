@@ -153,6 +153,19 @@ def test_fate_wrapper_matches_the_executed_reference(it):
     print("_fate vs reference: worst", ivp_util.check_fate(ivp_util.load(), it, 1e-8))
 
 
+def test_sliced_cell_sets_on_the_device(it, monkeypatch):
+    rng = np.random.default_rng(21)
+    vf = {"X_ctrl": rng.normal(size=(40, 4)), "C": rng.normal(size=(40, 4)) * 0.3, "beta": 0.2}
+    y0, t = rng.normal(size=(23, 4)), np.linspace(0, 4.0, 7)
+    f = it.RkhsField(vf)
+    whole = it.integrate_vf_ivp(y0, t, "both", f, interpolation_num=50, sampling="logspace")
+    monkeypatch.setattr(it, "RESIDENT_BYTES", 2 * 9 * it._resident_bytes_per_cell(t, 50, 4))      # nine cells per slice
+    sliced = it.integrate_vf_ivp(y0, t, "both", f, interpolation_num=50, sampling="logspace")
+    assert len(sliced[1]) == 23
+    for a, b in zip(whole[0] + whole[1], sliced[0] + sliced[1]):
+        assert np.array_equal(a, b)
+
+
 def test_svc_integrate_method(it):
     from dynamo_release_b200 import SvcVectorField
 

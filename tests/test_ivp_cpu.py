@@ -115,6 +115,34 @@ def test_start_at_rest_like_scipy():
     assert np.array_equal(r.sol(np.array([0.0, 5e-7])), io.dense_eval(g, np.array([0.0, 5e-7])))
 
 
+def test_large_cell_sets_are_sliced_without_changing_results(monkeypatch):
+    """More cells than the HBM budget for resident dense solutions: solve -> resample -> evaluate runs per slice."""
+    from dynamo_release_b200 import integrate as it
+
+    calls = []
+    base = ivp_util.oracle_batch(it.DenseSolution, it.IvpResult)
+
+    def counting(init_states, *a, **k):
+        calls.append(len(init_states))
+        return base(init_states, *a, **k)
+
+    monkeypatch.setattr(it, "solve_ivp_batch", counting)
+    z = ivp_util.load()
+    f = it.RkhsField(ivp_util.field(z, "sink"))
+    init, t = z["sink/init"], np.linspace(0, 3.0, 7)
+    whole = it.integrate_vf_ivp(init, t, "both", f, interpolation_num=40, sampling="arc_length")
+    assert calls == [5, 5]
+    calls.clear()
+    monkeypatch.setattr(it, "RESIDENT_BYTES", 2 * 2 * it._resident_bytes_per_cell(t, 40, 3))     # two cells per slice
+    sliced = it.integrate_vf_ivp(init, t, "both", f, interpolation_num=40, sampling="arc_length")
+    assert calls == [2, 2, 2, 2, 1, 1]
+    for a, b in zip(whole[0] + whole[1], sliced[0] + sliced[1]):
+        assert np.array_equal(a, b)
+    calls.clear()
+    it.integrate_vf_ivp(init, t, "forward", f, interpolation_num=40, sampling="uniform_indices")
+    assert calls == [5]          # one shared time grid: never sliced
+
+
 def test_no_initial_states_gives_empty_lists():
     from dynamo_release_b200.integrate import RkhsField, integrate_vf_ivp
 
