@@ -2,8 +2,6 @@
 // acceleration / curvature).  FP64 throughout; control points and coefficients are staged in shared
 // memory in chunks and broadcast to the threads, cells stream from HBM.
 #include "common.cuh"
-#include "tma.cuh"
-#include <cstdlib>
 
 namespace dvf {
 
@@ -181,15 +179,13 @@ __global__ void __launch_bounds__(128) k_eval(const double* __restrict__ x, int6
     }
 }
 
-// PARK: the kernel values k_m of the first pass are parked in `kpark` ([CTA][m][thread], coalesced) and read back by the
-// second pass instead of being recomputed (distances + exp: 50 of its 140 FP64 instructions per cell and control point)
-template <int DP, bool PARK>
+template <int DP>
 __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64_t n, int D,
                                              const double* __restrict__ Xc, int M, double beta,
                                              const double* __restrict__ C, int formula, double* __restrict__ v_out,
                                              double* __restrict__ div_out, double* __restrict__ acc_out,
                                              double* __restrict__ accn_out, double* __restrict__ curv_out,
-                                             double* __restrict__ curvn_out, double* __restrict__ kpark) {
+                                             double* __restrict__ curvn_out) {
     __shared__ double cs[ev_chunk<DP>::MC * DP];
     __shared__ double Cs[ev_chunk<DP>::MC * DP];
     const int64_t cell = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -215,7 +211,6 @@ __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64
                 t2b = fma(tb, Cs[m * DP + d + 1], t2b);
             }
             const double k = exp(-beta * (d2a + d2b));
-            if (PARK) kpark[((int64_t)blockIdx.x * M + m0 + m) * 128 + threadIdx.x] = k;
             div = fma(k, t2a + t2b, div);
 #pragma unroll
             for (int d = 0; d < DP; ++d) vr[d] = fma(k, Cs[m * DP + d], vr[d]);
@@ -235,19 +230,15 @@ __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64
             __syncthreads();
             for (int m = 0; m < mc; ++m) {
                 double d2a = 0.0, d2b = 0.0, sa = 0.0, sb = 0.0;
-                double kp = 0.0;
-                if (PARK) kp = kpark[((int64_t)blockIdx.x * M + m0 + m) * 128 + threadIdx.x];
 #pragma unroll
                 for (int d = 0; d < DP; d += 2) {
                     double ta = xr[d] - cs[m * DP + d], tb = xr[d + 1] - cs[m * DP + d + 1];
-                    if (!PARK) {
-                        d2a = fma(ta, ta, d2a);
-                        d2b = fma(tb, tb, d2b);
-                    }
+                    d2a = fma(ta, ta, d2a);
+                    d2b = fma(tb, tb, d2b);
                     sa = fma(ta, vr[d], sa);
                     sb = fma(tb, vr[d + 1], sb);
                 }
-                const double ks = (PARK ? kp : exp(-beta * (d2a + d2b))) * (sa + sb);
+                const double ks = exp(-beta * (d2a + d2b)) * (sa + sb);
 #pragma unroll
                 for (int d = 0; d < DP; ++d) ar[d] = fma(ks, Cs[m * DP + d], ar[d]);
             }
@@ -515,24 +506,11 @@ extern "C" int dvf_div_acc_curv(const double* x, int64_t n, int D, const double*
         DVF_LAUNCH_CHECK();
         return DVF_OK;
     }
-    // second pass wanted and the parked kernel values fit a modest scratch (stream-ordered pool): 4 GB at 1M x 500
-    const unsigned blocks = (unsigned)((n + 127) / 128);
-    const size_t park_bytes = (size_t)blocks * 128 * (size_t)M * sizeof(double);
-    static const bool park_off = getenv("DVF_DAC_NOPARK") != nullptr;       // developer experiments
-    const bool park = (acc || acc_norm || curv || curv_norm) && park_bytes <= ((size_t)8 << 30) && !park_off;
-    void* kp = nullptr;
-    if (park) { if (int rc = pool_alloc(&kp, park_bytes, (cudaStream_t)stream)) return rc; }
-    const int rc = dispatch_dp(D, [&](auto dp) {
+    return dispatch_dp(D, [&](auto dp) {
         constexpr int DP = decltype(dp)::value;
-        if (park)
-            k_dac<DP, true><<<blocks, 128, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, formula, v, div, acc, acc_norm,
-                                                                    curv, curv_norm, (double*)kp);
-        else
-            k_dac<DP, false><<<blocks, 128, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, formula, v, div, acc, acc_norm,
-                                                                     curv, curv_norm, nullptr);
+        k_dac<DP><<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, formula, v, div,
+                                                                              acc, acc_norm, curv, curv_norm);
         DVF_LAUNCH_CHECK();
         return DVF_OK;
     });
-    if (kp) cudaFreeAsync(kp, (cudaStream_t)stream);
-    return rc;
 }
