@@ -196,3 +196,21 @@ def test_threaded_scipy_fft_equals_numpy_fft_bitwise():
         got = scipy.fft.rfft(a[:, lo:hi], axis=1, workers=4)
         ref = np.stack([[np.fft.rfft(a[i, lo:hi, k]) for k in range(7)] for i in range(37)]).transpose(0, 2, 1)
         assert np.array_equal(got, ref)
+
+
+def test_time_sequence_helpers_equal_the_reference():
+    """svc._t_end / _t_seq against the executed getTend / getTseq (tools/utils.py:3175-3209); build container only."""
+    from oracle import ref_loader
+
+    if not ref_loader.available():
+        pytest.skip("reference tree not present")
+    tu = ref_loader.load("dynamo.tools.utils")
+    from dynamo_release_b200.svc import _t_end, _t_seq
+
+    rng = np.random.default_rng(4)
+    X, V = rng.normal(size=(500, 7)) * 3, rng.normal(size=(500, 7)) * 0.1
+    V[::17] = 0.0
+    assert _t_end(X, V) == tu.getTend(X, V)
+    for init_cols, t_end, step in ((7, 250.0, None), (7, 12345.6, None), (400, 1e9, None), (7, 30.0, 0.5), (7, 3.0, 1)):
+        init = np.zeros((3, init_cols))
+        assert np.array_equal(_t_seq(init, t_end, step), tu.getTseq(init, t_end, step))
