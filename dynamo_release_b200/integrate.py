@@ -7,8 +7,10 @@ right-hand-side call being a NumPy `vector_field_function`; here every trajector
 and dense output on the device.  The sampling of the finished trajectories (arc length / log space / uniform indices)
 is the reference's host-side bookkeeping, restated below with the same NumPy / SciPy calls it makes.
 
-The field must be this package's RKHS field (an object carrying `vf_dict`, e.g. SvcVectorField.func); there is no
-CPU fallback for arbitrary Python callables.
+The field must be this package's RKHS field: an object carrying `vf_dict` (SvcVectorField.func), or the plain
+function dynamo itself builds around vector_field_function (`lambda x: scale * vector_field_function(x, VecFld, dims)`,
+prediction/fate.py:133-135), which is recognised by tracing it (_field_of).  There is no CPU fallback for arbitrary
+Python callables.
 """
 from __future__ import annotations
 
@@ -132,14 +134,65 @@ class IvpResult:
         self.t, self.y, self.sol, self.status = t, y, sol, status
 
 
-def _field_of(f):
+def _exact_scale(s, pairs):
+    """The factor the callable multiplied the field by: the float next to the ratio s for which factor * field
+    reproduces the callable's outputs bit for bit (the ratio of two rounded numbers can be one ulp off)."""
+    cands = [s, np.nextafter(s, np.inf), np.nextafter(s, -np.inf)] + [float(np.round(s, k)) for k in range(16)]
+    for c in cands:
+        if all(np.array_equal(c * r, o) for r, o in pairs):
+            return float(c)
+    return float(s)
+
+
+def _field_of(f, probes=None):
+    """(vf_dict, scale) of the field behind the callable `f`.  Objects carrying `vf_dict` (RkhsField, what
+    SvcVectorField.func / vecfld_from_adata return) are taken as they are.  A plain function -- dynamo builds
+    `lambda x: scale * vector_field_function(x=x, vf_dict=VecFld, dim=dims)` in prediction/fate.py:133-135 and
+    scVectorField.py:764-766 -- is called on a few of the initial states with a trace open on vector_field_function
+    (vf._TRACE): if every call evaluated one and the same RKHS field over all its dimensions and the output is one
+    constant times that value, the callable IS scale x field and runs on the device.  Anything else is refused: there
+    is no CPU path for arbitrary Python callables."""
+    from . import vf as _vf
+
     vf_dict = getattr(f, "vf_dict", None)
-    if vf_dict is None:
-        raise NotImplementedError(
-            "integrate_vf_ivp on the B200 backend integrates this package's RKHS field (an object carrying vf_dict, "
-            "e.g. SvcVectorField.func / RkhsField); arbitrary Python callables have no device path and there is no "
-            "CPU fallback")
-    return vf_dict, float(getattr(f, "scale", 1.0))
+    if vf_dict is not None:
+        return vf_dict, float(getattr(f, "scale", 1.0))
+    refuse = NotImplementedError(
+        "integrate_vf_ivp on the B200 backend integrates this package's RKHS field: pass an object carrying vf_dict "
+        "(SvcVectorField.func / RkhsField) or a function of the form `lambda x: scale * vector_field_function(x, vf_dict)`; "
+        "other Python callables have no device path and there is no CPU fallback")
+    if probes is None or len(probes) == 0 or not callable(f):
+        raise refuse
+    pairs, fields = [], []
+    for x in np.atleast_2d(probes)[:3]:
+        _vf._TRACE.rec = rec = []
+        try:
+            out = np.asarray(f(np.array(x, dtype=np.float64)))
+        finally:
+            _vf._TRACE.rec = None
+        if len(rec) != 1:
+            raise refuse
+        d, dim, ctrl_ind, res = rec[0]
+        res = np.asarray(res)
+        n_dim = np.shape(d["X_ctrl"])[1]
+        full = dim is None or (np.isscalar(dim) and dim == n_dim) or \
+            (not np.isscalar(dim) and list(np.atleast_1d(dim)) == list(range(n_dim)))
+        if ctrl_ind is not None or not full or out.shape != res.shape:
+            raise refuse
+        fields.append(d)
+        pairs.append((res, out))
+    if any(d is not fields[0] for d in fields):
+        raise refuse
+    ratios = [o.flat[np.argmax(np.abs(r))] / r.flat[np.argmax(np.abs(r))] for r, o in pairs if np.any(r != 0)]
+    if not ratios:
+        if all(not np.any(o) for _, o in pairs):
+            return fields[0], 1.0              # the field vanishes at the probes and so does the callable
+        raise refuse
+    s = ratios[0]
+    for r, o in pairs:
+        if not np.allclose(o, s * r, rtol=1e-12, atol=0.0):
+            raise refuse                        # not a constant multiple of the field
+    return fields[0], _exact_scale(s, pairs)
 
 
 def solve_ivp_batch(init_states, vf_dict, t_span, max_step, scale=1.0, rtol=RTOL, atol=ATOL, cap=None):
@@ -307,13 +360,14 @@ def integrate_vf_ivp(init_states, t, integration_direction, f, args=None, interp
                      sampling="arc_length", verbose=False, disable=False):
     """reference prediction/utils.py:62-259.  Returns (t, Y): lists with one time vector and one (D, n_points) array
     per initial state."""
-    vf_dict, scale = _field_of(f)
     init_states = np.asarray(init_states)
     if init_states.ndim == 1:
         init_states = init_states[None, :]
     n_cell, n_feature = init_states.shape
     if n_cell == 0:
         return [], []                       # the reference's per-cell loops do not run
+    vf_dict, scale = _field_of(f, init_states)
+    f = ScaledRkhsField(vf_dict, scale)     # what the callable was recognised as (slices below do not trace again)
     t = np.asarray(t)
     if integration_direction not in ("forward", "backward", "both"):
         raise Exception("both, forward, backward are the only valid direction argument strings")

@@ -8,6 +8,8 @@ Pass `device_out=True` to keep results on the GPU as torch tensors (benchmark / 
 """
 from __future__ import annotations
 
+import threading
+
 import numpy as np
 import torch
 
@@ -50,6 +52,19 @@ def con_K(x, y, beta=0.1, method="cdist", return_d=False, timeit=False, device_o
     return _out(K, device_out)
 
 
+# Field tracing (integrate.py): dynamo wraps the field in plain lambdas, e.g. `lambda x: scale * vector_field_function(
+# x=x, vf_dict=VecFld, dim=dims)` (prediction/fate.py:133-135, scVectorField.py:764-766).  While a trace is open on this
+# thread every call of vector_field_function notes which field it evaluated and what it returned, so the integrator can
+# recognise such a callable as "scale x this RKHS field" and run it on the device.
+_TRACE = threading.local()
+
+
+def _record_trace(vf_dict, dim, X_ctrl_ind, result):
+    rec = getattr(_TRACE, "rec", None)
+    if rec is not None:
+        rec.append((vf_dict, dim, X_ctrl_ind, result))
+
+
 def vector_field_function(x, vf_dict, dim=None, kernel="full", X_ctrl_ind=None, timeit=False, device_out=False,
                           **kernel_kwargs):
     """reference vectorfield/utils.py:73-142:  f(x) = K(x, X_ctrl) C."""
@@ -68,7 +83,9 @@ def vector_field_function(x, vf_dict, dim=None, kernel="full", X_ctrl_ind=None, 
         v = v.reshape(-1)  # con_K flattens a single row (:196-197), so K.dot(C) is 1-d
     if dim is not None:
         v = v[..., :dim] if np.isscalar(dim) else v[..., dim]
-    return _out(v, device_out)
+    res = _out(v, device_out)
+    _record_trace(vf_dict, dim, X_ctrl_ind, res)
+    return res
 
 
 class RkhsJacobian:

@@ -166,6 +166,24 @@ def test_sliced_cell_sets_on_the_device(it, monkeypatch):
         assert np.array_equal(a, b)
 
 
+def test_lambda_wrapped_field_runs_on_the_device(it):
+    """The callable dynamo's fate() builds (prediction/fate.py:133-135) around the package's vector_field_function."""
+    import dynamo_release_b200 as dvf
+
+    rng = np.random.default_rng(31)
+    vf = {"X_ctrl": rng.normal(size=(40, 4)), "C": rng.normal(size=(40, 4)) * 0.3, "beta": 0.2}
+    y0, t = rng.normal(size=(10, 4)), np.linspace(0, 4.0, 7)
+    scale, dims = 0.7, None
+    a = it._fate(lambda x: scale * dvf.vector_field_function(x=x, vf_dict=vf, dim=dims), y0, t_end=4.0, step_size=0.5,
+                 direction="both", interpolation_num=30, average=False, sampling="arc_length")
+    b = it._fate(it.ScaledRkhsField(vf, scale), y0, t_end=4.0, step_size=0.5, direction="both", interpolation_num=30,
+                 average=False, sampling="arc_length")
+    for u, v in zip(a[0] + a[1], b[0] + b[1]):
+        assert np.array_equal(u, v)
+    with pytest.raises(NotImplementedError):
+        it.integrate_vf_ivp(y0, t, "forward", lambda x: -x)
+
+
 def test_svc_integrate_method(it):
     from dynamo_release_b200 import SvcVectorField
 

@@ -157,6 +157,50 @@ def test_generic_callable_is_refused():
         integrate_vf_ivp(np.zeros((1, 2)), np.linspace(0, 1, 3), "forward", lambda x: x)
 
 
+def _traced_vff(x, vf_dict, dim=None, X_ctrl_ind=None):
+    """Stand-in for the package's vector_field_function on a box without CUDA: oracle arithmetic, same trace hook."""
+    from dynamo_release_b200 import vf as vfm
+
+    r = vo.field_eval(x, vf_dict)
+    if dim is not None:
+        r = r[..., :dim] if np.isscalar(dim) else r[..., dim]
+    vfm._record_trace(vf_dict, dim, X_ctrl_ind, r)
+    return r
+
+
+def test_lambda_wrapped_fields_are_recognised(monkeypatch):
+    """dynamo hands integrate_vf_ivp `lambda x: scale * vector_field_function(x=x, vf_dict=VecFld, dim=dims)`
+    (prediction/fate.py:133-135): the trace recovers the field and the exact scale, and refuses everything else."""
+    from dynamo_release_b200 import integrate as it
+
+    rng = np.random.default_rng(8)
+    vf = {"X_ctrl": rng.normal(size=(20, 3)), "C": rng.normal(size=(20, 3)), "beta": 0.3}
+    other = {"X_ctrl": vf["X_ctrl"], "C": 2 * vf["C"], "beta": 0.3}
+    probes = rng.normal(size=(5, 3))
+    for scale in (1, 2.5, 0.1, 1 / 3, 1e-3, -7.0):
+        for dims in (None, 3, [0, 1, 2]):
+            d, s = it._field_of(lambda x: scale * _traced_vff(x=x, vf_dict=vf, dim=dims), probes)
+            assert d is vf and s == float(scale)
+    refused = [lambda x: x,                                                        # never touches the field
+               lambda x: _traced_vff(x, vf) * x[0],                                # not a constant multiple
+               lambda x: _traced_vff(x, vf) + 1.0,
+               lambda x: _traced_vff(x, vf, dim=2),                                # a subset of the dimensions
+               lambda x: _traced_vff(x, vf, X_ctrl_ind=[0, 1]),
+               lambda x: _traced_vff(x, vf) + _traced_vff(x, other),              # two evaluations
+               lambda x: _traced_vff(x, vf if x[0] > probes[1, 0] else other)]     # different fields per call
+    for g in refused:
+        with pytest.raises(NotImplementedError):
+            it._field_of(g, probes)
+    # and end to end (oracle standing in for the device solver): same lists as with the field object
+    monkeypatch.setattr(it, "solve_ivp_batch", ivp_util.oracle_batch(it.DenseSolution, it.IvpResult))
+    t = np.linspace(0, 2.0, 5)
+    a = it.integrate_vf_ivp(probes, t, "forward", lambda x: 2.5 * _traced_vff(x=x, vf_dict=vf, dim=None),
+                            interpolation_num=20, sampling="logspace")
+    b = it.integrate_vf_ivp(probes, t, "forward", it.ScaledRkhsField(vf, 2.5), interpolation_num=20, sampling="logspace")
+    for u, v in zip(a[0] + a[1], b[0] + b[1]):
+        assert np.array_equal(u, v)
+
+
 def test_repeat_cut_equals_the_reference_on_periodic_trajectories():
     """The batched restatement of dup_osc_idx_iter (vectorfield/topography.py:332-397) against the executed reference,
     on limit-cycle-like curves where the cut really fires (several lengths, several periods, plus noise and a drift that
