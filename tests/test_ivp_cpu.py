@@ -258,3 +258,30 @@ def test_time_sequence_helpers_equal_the_reference():
     for init_cols, t_end, step in ((7, 250.0, None), (7, 12345.6, None), (400, 1e9, None), (7, 30.0, 0.5), (7, 3.0, 1)):
         init = np.zeros((3, init_cols))
         assert np.array_equal(_t_seq(init, t_end, step), tu.getTseq(init, t_end, step))
+
+
+def test_svc_integrate_method_equals_the_reference_method(monkeypatch):
+    """SvcVectorField.integrate (scVectorField.py:721-784) incl. the default t_end of getTend, against the executed
+    reference class on its own fit; the oracle stands in for the device solver.  Build container only."""
+    from oracle import ref_loader
+
+    if not ref_loader.available():
+        pytest.skip("reference tree not present")
+    sc = ref_loader.load("dynamo.vectorfield.scVectorField")
+    from dynamo_release_b200 import integrate as it
+    from dynamo_release_b200.svc import SvcVectorField
+
+    rng = np.random.default_rng(12)
+    X = rng.normal(size=(300, 3))
+    V = -(X - 0.2) + 0.05 * rng.normal(size=X.shape)
+    ref = sc.SvcVectorField(X, V, None, M=30, MaxIter=20, normalize=False)
+    ref.train()
+    want = ref.integrate(X[:4], interpolation_num=20, sampling="logspace", integration_direction="both", disable=True)
+    monkeypatch.setattr(it, "solve_ivp_batch", ivp_util.oracle_batch(it.DenseSolution, it.IvpResult))
+    vf = {k: ref.vf_dict[k] for k in ("X_ctrl", "C", "beta")}
+    ours = SvcVectorField(vf_dict=vf, func=it.RkhsField(vf))
+    ours.data["X"], ours.data["V"] = ref.get_X(), ref.get_V()
+    got = ours.integrate(X[:4], interpolation_num=20, sampling="logspace", integration_direction="both", disable=True)
+    assert len(got[1]) == len(want[1]) == 4
+    for a, b in zip(got[0] + got[1], want[0] + want[1]):
+        assert np.shape(a) == np.shape(b) and rel(a, b) < 1e-10
