@@ -76,11 +76,17 @@ def rel(a, b):
     return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
 
 
-def make_case(name, X, V, params, n_jac=48, n_calc=200, n_genes=24, gene_cells=32, lean=None):
-    """lean=(n, d, seed, vscale): inputs are NOT stored; tests regenerate them with
-    vfc_oracle.hematopoiesis_like(n, d, seed) * vscale and check the stored checksums."""
+LHS_ROWS = 24    # big-M cases keep this many rows of lhs per iteration (plus its column sums) instead of M x M
+
+
+def make_case(name, X, V, params, n_jac=48, n_calc=200, n_genes=24, gene_cells=32, lean=None, keep_iters=(0, 1),
+              lhs_full=True):
+    """lean=(n, d, seed, vscale[, manifold_seed]): inputs are NOT stored; tests regenerate them (4 values:
+    vfc_oracle.hematopoiesis_like(n, d, seed) * vscale; 5 values: the bench's generator
+    dynamo_release_b200.datasets.hematopoiesis_like with that manifold seed) and check the stored checksums.
+    lhs_full=False: per kept iteration only LHS_ROWS evenly spaced rows of lhs and its column sums are stored."""
     sc, vfu, _ = ref_loader.hot_path()
-    vf, d, tr = run_reference_fit(sc, X, V, **params)
+    vf, d, tr = run_reference_fit(sc, X, V, keep_iters=keep_iters, **params)
     out = {"meta": np.array(_versions()), "params_keys": np.array(list(params.keys())),
            "params_vals": np.array([float(v) for v in params.values()])}
     if lean is None:
@@ -103,8 +109,17 @@ def make_case(name, X, V, params, n_jac=48, n_calc=200, n_genes=24, gene_cells=3
     out["trace_sigma2_in"] = np.array(tr["sigma2_in"])
     out["trace_gamma_in"] = np.array(tr["gamma_in"])
     out["trace_E_data"] = np.array(tr["E_data"])
+    out["trace_kept_iters"] = np.array(sorted(tr["lhs"].keys()))
     for it_no in tr["lhs"]:
-        out["trace_lhs_%d" % it_no] = tr["lhs"][it_no]
+        if lhs_full:
+            out["trace_lhs_%d" % it_no] = tr["lhs"][it_no]
+        else:
+            lhs = tr["lhs"][it_no]
+            rows = np.linspace(0, lhs.shape[0] - 1, LHS_ROWS).astype(np.int64)
+            out["trace_lhs_rows_idx"] = rows
+            out["trace_lhs_rows_%d" % it_no] = lhs[rows]
+            out["trace_lhs_colsum_%d" % it_no] = lhs.sum(0)
+            out["trace_lhs_cond_%d" % it_no] = np.array(np.linalg.cond(lhs))
         out["trace_rhs_%d" % it_no] = tr["rhs"][it_no]
         out["trace_C_%d" % it_no] = tr["C"][it_no]
         out["trace_P_%d" % it_no] = tr["P"][it_no] if lean is None else tr["P"][it_no][::37]
@@ -137,7 +152,10 @@ def make_case(name, X, V, params, n_jac=48, n_calc=200, n_genes=24, gene_cells=3
 
     # reference-vs-itself floor: permute the cells and refit
     perm = np.random.default_rng(99).permutation(len(X))
-    _, d2, _ = run_reference_fit(sc, X[perm], V[perm], **params)
+    _, d2, tr2 = run_reference_fit(sc, X[perm], V[perm], keep_iters=(), **params)
+    out["floor_E_traj"] = np.asarray(d2["E_traj"])
+    out["floor_sigma2"] = np.array(d2["sigma2"])
+    out["floor_trace_sigma2_in"] = np.array(tr2["sigma2_in"])
     same_ctrl = d2["X_ctrl"].shape == d["X_ctrl"].shape and np.array_equal(d2["X_ctrl"], d["X_ctrl"])
     out["floor_same_ctrl"] = np.array(same_ctrl)
     out["floor_iteration"] = np.array(d2["iteration"])
@@ -173,8 +191,25 @@ def lean_case(name, n, d, seed, vscale, params, **kw):
     make_case(name, X, V, params, lean=(n, d, seed, vscale), **kw)
 
 
+def bench_case(name, n, d, seed, vscale, manifold_seed, params, **kw):
+    """Cases at the configurations bench.py quotes its numbers on, from bench.py's own generator."""
+    from dynamo_release_b200.datasets import hematopoiesis_like
+
+    X, V = hematopoiesis_like(n, d, seed=seed, velocity_scale=vscale, manifold_seed=manifold_seed)
+    make_case(name, X, V, params, lean=(n, d, seed, vscale, manifold_seed), keep_iters=(0, 1, 2, 3), lhs_full=False,
+              n_jac=24, n_calc=100, gene_cells=16, **kw)
+
+
 def main():
     only = sys.argv[1:]
+    if "bench" in only or not only:
+        # BASELINE.json configs[1] exactly (C2), a C3-shaped case (M = 500) and a C5-shaped case (D = 50, M = 1000):
+        # bench.py's generator, seed (100 = rank 0) and velocity_scale
+        bench_case("c2_n100000_d30_m100", 100000, 30, 100, 0.05, 7, dict(M=100, MaxIter=30))
+        bench_case("c3s_n50000_d30_m500", 50000, 30, 100, 0.05, 7, dict(M=500, MaxIter=30))
+        bench_case("c5s_n20000_d50_m1000", 20000, 50, 100, 0.05, 7, dict(M=1000, MaxIter=10))
+        if only:
+            return
     if "lean" in only or not only:
         # non-degenerate EM (sigma2 small enough that P is not clamped everywhere; far outliers hit the t1 == 0 rule)
         lean_case("lean_n20000_d30_m100", 20000, 30, 11, 0.05, dict(M=100, MaxIter=30))

@@ -1,7 +1,11 @@
 """TEST INFRASTRUCTURE ONLY -- loader that executes the UNMODIFIED reference source.
 
-Nothing in the product package may import this file.  Allowed importers: tests/,
-oracle/gen_golden.py, (never bench.py on the GPU box: /root/reference does not exist there).
+Nothing in the product package may import this file.  Allowed importers: tests/, oracle/gen_golden*.py,
+__graft_entry__.smoke() and bench.py's `cpu_baseline` / `--impl reference` legs.
+
+Where the reference comes from: /root/reference in the build container; on the GPU box (where that path does not
+exist) the byte-for-byte staged copy oracle/_ref/ (git-ignored, shipped with the snapshot; oracle/stage_ref.py
+writes it during build()).  `source()` says which one is in use.
 
 What it does
 ------------
@@ -30,7 +34,20 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("DVF_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+STAGED_ROOT = os.path.join(_HERE, "_ref")
+
+
+def _pick_root():
+    env = os.environ.get("DVF_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/dynamo/vectorfield"):
+        return "/root/reference"
+    return STAGED_ROOT
+
+
+REFERENCE_ROOT = _pick_root()
 
 # third-party roots that are absent here and only used for non-numeric side effects
 _STUB_ROOTS = {
@@ -149,6 +166,27 @@ _installed = False
 
 def available() -> bool:
     return os.path.isdir(os.path.join(REFERENCE_ROOT, "dynamo", "vectorfield"))
+
+
+def source() -> str:
+    """'reference' (the tree itself), '_ref' (the staged byte-for-byte copy) or 'absent'."""
+    if not available():
+        return "absent"
+    return "_ref" if os.path.abspath(REFERENCE_ROOT) == os.path.abspath(STAGED_ROOT) else "reference"
+
+
+def verify_staged() -> int:
+    """Check every staged file against the sha256 recorded when it was copied; returns the number of files."""
+    import hashlib
+    import json
+
+    with open(os.path.join(STAGED_ROOT, "MANIFEST.json")) as f:
+        man = json.load(f)["files"]
+    for rel_path, digest in man.items():
+        with open(os.path.join(STAGED_ROOT, rel_path), "rb") as f:
+            if hashlib.sha256(f.read()).hexdigest() != digest:
+                raise RuntimeError("staged reference file %s was modified" % rel_path)
+    return len(man)
 
 
 def install():

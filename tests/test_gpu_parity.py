@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 import torch
 
-from golden_util import CASES, Golden, rel
+from golden_util import CASES, Golden, prefix_len, rel
 from oracle import vfc_oracle as o
 
 pytestmark = pytest.mark.gpu
@@ -140,7 +140,7 @@ def test_em_steps_teacher_forced(pkg, name):
     assert np.array_equal(_np(UY[:, M:M + D]), Y) and float(UY[:, M + D:].abs().sum()) == 0.0
     Kc = o.gauss_kernel(Xc, Xc, beta)
     r2 = np.sum(Y**2, 1)
-    for it in (0, 1):
+    for it in g.kept_iters():
         sigma2, gamma = float(g["trace_sigma2_in"][it]), float(g["trace_gamma_in"][it])
         P, stats = k.estep(r2, D, sigma2, gamma, p["a"])
         assert rel(_np(P)[::s], g["trace_P_%d" % it].reshape(-1)) < 1e-11
@@ -148,13 +148,14 @@ def test_em_steps_teacher_forced(pkg, name):
         G = _np(k.gram(UY, P, p["minP"], D, M))
         lhs = np.tril(G[:M, :M]) + np.tril(G[:M, :M], -1).T + p["lambda_"] * sigma2 * Kc
         rhs = G[M:M + D, :M].T
-        assert rel(lhs, g["trace_lhs_%d" % it]) < 1e-12
+        assert g.lhs_check(it, lhs) < 1e-12
         assert rel(rhs, g["trace_rhs_%d" % it]) < 1e-12
-        # solver: closer to the exact solution of the reference's system than the reference's own result
+        # solver (Cholesky of lhs): closer to the exact solution of the reference's system than the reference's own
+        # normal-equations result
         C_gpu, info = k.solve(G, Kc, M, D, p["lambda_"] * sigma2)
         assert info == 0
         C_gpu = _np(C_gpu)
-        C_exact = _exact_solve(g["trace_lhs_%d" % it], g["trace_rhs_%d" % it])
+        C_exact = _exact_solve(lhs, g["trace_rhs_%d" % it])
         err_gpu, err_ref = rel(C_gpu, C_exact), rel(g["trace_C_%d" % it], C_exact)
         assert err_gpu <= max(1e-9, 2 * err_ref), (err_gpu, err_ref)
         # continue from the REFERENCE's C (teacher forcing): V = U C, r2, sum P r2
@@ -166,15 +167,30 @@ def test_em_steps_teacher_forced(pkg, name):
         assert rel(_np(r2_t), r2) < 1e-10
         Pc = np.maximum(_np(P), p["minP"])
         assert rel(_np(st)[0], Pc.dot(r2)) < 1e-11
-        if it == 0:
-            assert rel(Pc.dot(r2) / (Pc.sum() * D), g["trace_sigma2_in"][1]) < 1e-10
+        if it + 1 < len(g["trace_sigma2_in"]):
+            assert rel(Pc.dot(r2) / (Pc.sum() * D), g["trace_sigma2_in"][it + 1]) < 1e-10
+
+
+def _e2e_report(g, vf, name):
+    """relE per iteration against the reference and against the reference's own permuted refit (the floor)."""
+    E_ref, E_floor, E = g["final_E_traj"], g["floor_E_traj"], vf["E_traj"]
+    m = min(len(E_ref), len(E))
+    ours = np.abs(E[:m] - E_ref[:m]) / np.abs(E_ref[:m])
+    mf = min(len(E_ref), len(E_floor))
+    floor = np.abs(E_floor[:mf] - E_ref[:mf]) / np.abs(E_ref[:mf])
+    return ours, floor
 
 
 @pytest.mark.parametrize("name", CASES)
 def test_fit_end_to_end(pkg, name):
+    """End-to-end fit against the executed reference.  Where the reference reproduces itself (permutation floor of V
+    below 1e-9) everything is gated at 1e-8 and iteration counts / index arrays are exact.  Elsewhere ("chaotic": the
+    normal-equations solve amplifies 1e-16 differences in lhs by cond(lhs)^2) nothing is waived:
+    the energy trajectory must stay within K x the deviation of the reference's OWN refit at every iteration (running
+    maximum), and V / sigma2 within K x the floor -- no absolute escape."""
+    K = 20.0
     g = Golden(name)
     fc, fv = g.floor()
-    tolC, tolV = max(1e-8, 50 * fc), max(1e-8, 50 * fv)
     vf = pkg.SvcVectorField(g.X.copy(), g.V.copy(), None, normalize=False, **g.params).train()
     s = g.stride
     assert np.array_equal(vf["ctrl_idx"], g["final_ctrl_idx"])
@@ -182,21 +198,35 @@ def test_fit_end_to_end(pkg, name):
     assert abs(vf["beta"] - float(g["final_beta"])) <= 1e-13 * vf["beta"]
     if not g.lean:
         assert np.array_equal(vf["valid_ind"], g["final_valid_ind"])
-    chaotic = fv > 1e-6 or name.startswith("toggle")
-    if not chaotic:
-        assert vf["iteration"] == int(g["final_iteration"])
-        assert rel(vf["E_traj"], g["final_E_traj"]) < tolV
-        assert rel(vf["sigma2"], g["final_sigma2"]) < max(tolV, 1e-8)
-        assert rel(vf["C"], g["final_C"]) < tolC
-        assert rel(vf["P"][::s], g["final_P"]) < max(tolV, 1e-8)
-        if not g.lean:
-            assert np.array_equal(vf["VFCIndex"], g["final_VFCIndex"])
     assert vf["P"].shape == (len(np.where(np.isfinite(g.V.sum(1)))[0]), 1)
     assert vf["V"].shape == g.X.shape and vf["normalize"] is False
-    dv = rel(vf["V"][::s], g["final_Vfit"])
-    print("\n[%s] iters %d (ref %d)  relV %.3g (floor %.3g)  relC %.3g (floor %.3g)"
-          % (name, vf["iteration"] + 1, int(g["final_iteration"]) + 1, dv, fv, rel(vf["C"], g["final_C"]), fc))
-    assert dv < (tolV if not chaotic else max(50 * fv, 1.0))
+    ours, floor = _e2e_report(g, vf, name)
+    same_ctrl = bool(g["floor_same_ctrl"])
+    chaotic = (fv > 1e-9) or not same_ctrl and name.startswith("toggle")
+    dv, dc = rel(vf["V"][::s], g["final_Vfit"]), rel(vf["C"], g["final_C"])
+    pre, pre_floor = prefix_len(vf["E_traj"], g["final_E_traj"]), g.floor_prefix()
+    print("\n[%s] iters %d (ref %d, ref refit %d)  relV %.3g (floor %.3g)  relC %.3g (floor %.3g)  E-prefix@1e-8 %d "
+          "(ref refit %d)\n    relE ours : %s\n    relE floor: %s"
+          % (name, vf["iteration"] + 1, int(g["final_iteration"]) + 1, int(g["floor_iteration"]) + 1, dv, fv, dc, fc,
+             pre, pre_floor, np.array2string(ours, precision=1), np.array2string(floor, precision=1)))
+    if not chaotic:
+        tolC, tolV = max(1e-8, K * fc), max(1e-8, K * fv)
+        assert vf["iteration"] == int(g["final_iteration"])
+        assert rel(vf["E_traj"], g["final_E_traj"]) < tolV
+        assert rel(vf["sigma2"], g["final_sigma2"]) < tolV
+        assert dc < tolC and dv < tolV
+        assert rel(vf["P"][::s], g["final_P"]) < tolV
+        if not g.lean:
+            assert np.array_equal(vf["VFCIndex"], g["final_VFCIndex"])
+        return
+    # chaotic: iteration prefix and K x floor, iteration by iteration
+    assert pre >= min(pre_floor, 1)
+    bound = np.maximum(1e-8, K * np.maximum.accumulate(np.concatenate([floor, np.full(max(0, len(ours) - len(floor)),
+                                                                                      floor.max())])))
+    assert np.all(ours <= bound[:len(ours)]), (ours, bound)
+    assert dv <= K * fv, (dv, fv)
+    fs = rel(float(g["floor_sigma2"]), float(g["final_sigma2"]))
+    assert rel(vf["sigma2"], float(g["final_sigma2"])) <= max(1e-8, K * fs)
 
 
 def test_fit_is_bitwise_reproducible(pkg):
