@@ -1,15 +1,24 @@
 #!/usr/bin/env python
 """bench.py -- cells/s for SparseVFC fit + per-cell Jacobian + divergence / acceleration / curvature.
 
-Workload (BASELINE.json configs[2], the one the metric is quoted on; fits one GPU): synthetic hematopoiesis-shaped
-1M cells x 30 PCs per GPU, M = 500 control points, MaxIter = 30.  N > 1: weak scaling, every rank holds 1M cells,
-ONE joint fit over N x 1M cells (NCCL allreduce of the Gram/RHS block per EM iteration), evaluation per rank.
+Workloads (BASELINE.json configs; synthetic hematopoiesis-shaped cells):
+  c3 (default, the one the metric is quoted on; fits one GPU): 1M cells x 30 PCs, M = 500 control points, MaxIter = 30
+  c2: 100k x 30, M = 100          c5: 4M x 50, M = 1000, exactly 10 EM iterations (the all-reduce scaling sweep)
+--scaling weak (default; what the driver's 1/2/4/8 run measures): every rank holds `cells` cells, ONE joint fit over
+N x cells (NCCL all-reduce of the Gram/RHS block per EM iteration), evaluation per rank.
+--scaling strong: `cells` is the TOTAL, split over the ranks (configs[2] "1M ... sharded across 8xB200", configs[4]).
 
-  value : whole-job cells/s with the inputs resident in HBM (CUDA events, max over ranks)
-  e2e   : the same job through the public numpy API (pinned host inputs -> numpy outputs, copies timed)
-  roofline : the dominant kernel (weighted Gram, FP64 tensor cores), CUDA-event timed inside the fit
-  cpu_baseline / --impl reference : the reference's algorithm (oracle port, NumPy/BLAS, all host threads) on a
-      bounded sample of the same workload.
+  value    : whole-job cells/s with the inputs resident in HBM (CUDA events, max over ranks)
+  e2e      : the same job through the public numpy API (pinned host inputs -> numpy outputs, copies timed); with N > 1
+             ranks it is ONE joint fit through the product API (SvcVectorField(..., sharded=True)), each rank
+             uploading its shard and downloading its shard's results
+  parity   : GPU against the executed reference -- the benchmarked outputs themselves (fixed C, a cell sample) and a
+             bounded refit of a subsample at the benchmark's M, next to the reference's own permutation floor
+  roofline : the dominant kernel (weighted Gram, FP64 tensor cores), CUDA-event timed inside the fit, against the FP64
+             DMMA peak measured in this run (tools/fp64_peak); `step` = SURVEY 8d's whole-step count
+  cpu_baseline / --impl reference : the UNMODIFIED reference (oracle/_ref, staged by build(); kind "reference") -- or the
+             NumPy port when the staged files are absent (kind "port") -- on a bounded sample of the same workload with
+             all host threads, its fit time rescaled to the EM iteration count the full-size job executes.
 One JSON line on stdout (rank 0).
 """
 from __future__ import annotations
@@ -29,7 +38,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 GRAM_DRAM_BYTES_NCU = 4.85e9    # k_gram_parts: 4.84 GB read + 7 MB written per launch (ncu --set full, profiles/ncu_k_gram_parts_r01_details.txt)
-FP64_PEAK_TFLOPS = 37.1   # DMMA m8n8k4 chain measured on this pool's B200 (tools/fp64_peak.cu, profiles/fp64_peak_r01.json)
+FP64_PEAK_FALLBACK = 37.1       # DMMA m8n8k4 chain, profiles/fp64_peak_r01.json -- used only if tools/fp64_peak cannot run
+
+# cells, D, M, MaxIter, ecr, EM iterations the full-size GPU job executes (reference-arm rescale target), default scaling
+WORKLOADS = {
+    "c3": dict(cells=1_000_000, pcs=30, ctrl=500, maxiter=30, ecr=1e-5, iters_full=8, scaling="weak",
+               ref_fit=30_000, ref_eval=1_000),
+    "c2": dict(cells=100_000, pcs=30, ctrl=100, maxiter=30, ecr=1e-5, iters_full=9, scaling="weak",
+               ref_fit=100_000, ref_eval=2_000),
+    "c5": dict(cells=4_000_000, pcs=50, ctrl=1000, maxiter=10, ecr=0.0, iters_full=10, scaling="strong",
+               ref_fit=12_000, ref_eval=400),
+}
 
 
 def parse():
@@ -38,56 +57,127 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cells", type=int, default=1_000_000, help="cells per GPU")
-    ap.add_argument("--pcs", type=int, default=30)
-    ap.add_argument("--ctrl", type=int, default=500)
-    ap.add_argument("--maxiter", type=int, default=30)
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--scaling", default=None, choices=["weak", "strong"])
+    ap.add_argument("--cells", type=int, default=None, help="cells per GPU (weak) / in total (strong)")
+    ap.add_argument("--pcs", type=int, default=None)
+    ap.add_argument("--ctrl", type=int, default=None)
+    ap.add_argument("--maxiter", type=int, default=None)
+    ap.add_argument("--ecr", type=float, default=None)
+    ap.add_argument("--lstsq", default="drouin", choices=["drouin", "cholesky"],
+                    help="M x M solver: the reference's normal-equations form (its default) or this backend's Cholesky")
     ap.add_argument("--velocity-scale", type=float, default=0.05)
+    ap.add_argument("--ref-iters", type=int, default=None,
+                    help="reference arm: EM iterations to rescale the sample's fit time to (default: what the full-size "
+                         "GPU job executes at this workload)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--no-parity", action="store_true")
+    a = ap.parse_args()
+    w = WORKLOADS[a.workload]
+    for k in ("cells", "pcs", "ctrl", "maxiter", "ecr"):
+        if getattr(a, k) is None:
+            setattr(a, k, w[k])
+    a.scaling = a.scaling or w["scaling"]
+    a.iters_full = a.ref_iters or w["iters_full"]
+    a.ref_fit, a.ref_eval = w["ref_fit"], w["ref_eval"]
+    return a
+
+
+METRIC = "cells/sec for SparseVFC fit + per-cell Jacobian/divergence/acceleration/curvature"
 
 
 def workload_name(a):
-    return ("synthetic hematopoiesis-shaped %d cells x %d PCs per GPU, M=%d ctrl pts, MaxIter=%d: SparseVFC fit + "
-            "jacobian + divergence + acceleration + curvature" % (a.cells, a.pcs, a.ctrl, a.maxiter))
+    per = "per GPU" if a.scaling == "weak" else "in total"
+    return ("%s: synthetic hematopoiesis-shaped %d cells x %d PCs %s, M=%d ctrl pts, MaxIter=%d, ecr=%g, lstsq_method=%s: "
+            "SparseVFC fit + jacobian + divergence + acceleration + curvature"
+            % (a.workload, a.cells, a.pcs, per, a.ctrl, a.maxiter, a.ecr, a.lstsq))
 
 
-# ----------------------------------------------------------------------------------------------------------
-# CPU baseline: the reference's algorithm (oracle/vfc_oracle.py, pinned against the executed reference by
-# tests/test_oracle_golden.py) on a bounded sample, all host threads available to BLAS.
-# ----------------------------------------------------------------------------------------------------------
-def cpu_reference_rate(a, n_iter_full=None, n_fit=50_000, n_eval=1_500):
-    from oracle import vfc_oracle as o
+def bench_data(a, n, seed):
     from dynamo_release_b200.datasets import hematopoiesis_like
 
-    X, V = hematopoiesis_like(n_fit, a.pcs, seed=1, velocity_scale=a.velocity_scale, manifold_seed=7)
+    return hematopoiesis_like(n, a.pcs, seed=seed, velocity_scale=a.velocity_scale, manifold_seed=7)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# The CPU side: the executed reference (oracle/ref_loader.py -> /root/reference here, the staged oracle/_ref on the GPU
+# box), or the NumPy port (oracle/vfc_oracle.py, pinned to the executed reference by tests/test_oracle_golden.py).
+# ----------------------------------------------------------------------------------------------------------
+class CpuReference:
+    def __init__(self, force_port=False):
+        from oracle import ref_loader
+
+        self.kind = "port"
+        self.source = "oracle/vfc_oracle.py (NumPy restatement)"
+        if ref_loader.available() and not force_port:
+            try:
+                self.sc, self.vfu, _ = ref_loader.hot_path()
+                self.kind = "reference"
+                self.source = {"_ref": "oracle/_ref (staged byte-for-byte copy of the reference files)",
+                               "reference": "/root/reference"}[ref_loader.source()]
+            except Exception as e:   # pragma: no cover
+                self.source += " [executed reference failed to load: %r]" % (e,)
+        if self.kind == "port":
+            from oracle import vfc_oracle
+
+            self.o = vfc_oracle
+
+    def fit(self, X, V, **kw):
+        """-> (VecFldDict, object with compute_* methods or None)"""
+        if self.kind == "reference":
+            obj = self.sc.SvcVectorField(X, V, None, normalize=False, **kw)
+            return obj.train(), obj
+        return self.o.train(X, V, **kw), None
+
+    def calculus(self, xs, vf, obj):
+        """Times of jacobian / divergence / acceleration / curvature on the cells xs, and the results."""
+        t, out = {}, {}
+        if self.kind == "reference":
+            t0 = time.perf_counter(); out["J"] = self.vfu.Jacobian_rkhs_gaussian(xs, vf); t["jacobian"] = time.perf_counter() - t0
+            t0 = time.perf_counter(); out["div"] = obj.compute_divergence(xs); t["divergence"] = time.perf_counter() - t0
+            t0 = time.perf_counter(); out["acc"], out["acc_mat"] = obj.compute_acceleration(xs); t["acceleration"] = time.perf_counter() - t0
+            t0 = time.perf_counter(); out["curv"], out["curv_mat"] = obj.compute_curvature(xs); t["curvature"] = time.perf_counter() - t0
+        else:
+            o = self.o
+            t0 = time.perf_counter(); out["J"] = o.jacobian(xs, vf); t["jacobian"] = time.perf_counter() - t0
+            t0 = time.perf_counter(); out["div"] = o.divergence(xs, vf); t["divergence"] = time.perf_counter() - t0
+            t0 = time.perf_counter(); r = o.acceleration(xs, vf); t["acceleration"] = time.perf_counter() - t0
+            out["acc"], out["acc_mat"] = r[2], r[3]
+            t0 = time.perf_counter(); out["curv"], out["curv_mat"] = o.curvature(xs, vf); t["curvature"] = time.perf_counter() - t0
+        return t, out
+
+    def field_object(self, vf):
+        """An object of the reference class carrying vf (for calculus on a fit that was not made by it)."""
+        if self.kind != "reference":
+            return None
+        obj = self.sc.SvcVectorField()
+        obj.vf_dict = vf
+        obj.func = lambda x: self.vfu.vector_field_function(x, vf)
+        return obj
+
+
+def cpu_reference_rate(a, n_iter_target, n_fit, n_eval, ref=None):
+    """cells/s of the CPU path on a bounded sample: fit of n_fit cells (its time rescaled from the iterations the
+    sample ran to `n_iter_target`, the count the full-size job executes) + calculus on n_eval cells; per-cell costs
+    added (every stage is linear in the number of cells: N-row GEMMs / per-cell loops)."""
+    ref = ref or CpuReference()
+    X, V = bench_data(a, n_fit, seed=1)
     t0 = time.perf_counter()
-    vf = o.train(X, V, M=a.ctrl, MaxIter=a.maxiter)
+    vf, obj = ref.fit(X, V, M=a.ctrl, MaxIter=a.maxiter, ecr=a.ecr)
     t_fit = time.perf_counter() - t0
-    iters = vf["iteration"] + 1
+    iters = int(vf["iteration"]) + 1
     xs = X[:n_eval]
-    t0 = time.perf_counter()
-    o.jacobian(xs, vf)
-    t_jac = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    o.divergence(xs, vf)
-    t_div = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    o.acceleration(xs, vf)
-    t_acc = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    o.curvature(xs, vf)
-    t_cur = time.perf_counter() - t0
-    # per-cell cost, linear in the number of cells (per-cell loops / N-row GEMMs); the fit is rescaled to the
-    # iteration count of the full-size run when it is known
-    fit_scale = (n_iter_full / iters) if n_iter_full else 1.0
-    per_cell = t_fit * fit_scale / n_fit + (t_jac + t_div + t_acc + t_cur) / n_eval
-    sample = ("fit on %d cells (%d EM iterations, %.2f s%s) + jacobian/divergence/acceleration/curvature on %d "
-              "cells (%.2f/%.2f/%.2f/%.2f s); per-cell costs added, linear extrapolation in cells"
-              % (n_fit, iters, t_fit, (", rescaled to %d iterations" % n_iter_full) if n_iter_full else "", n_eval,
-                 t_jac, t_div, t_acc, t_cur))
-    return 1.0 / per_cell, sample, t_fit + t_jac + t_div + t_acc + t_cur
+    t, _ = ref.calculus(xs, vf, obj)
+    fit_scale = (n_iter_target / iters) if n_iter_target else 1.0
+    per_cell = t_fit * fit_scale / n_fit + sum(t.values()) / n_eval
+    sample = ("%s: fit on %d cells (%d EM iterations, %.2f s, rescaled to %d iterations = the full-size job's count) + "
+              "jacobian/divergence/acceleration/curvature on %d cells (%.2f/%.2f/%.2f/%.2f s); per-cell costs added, "
+              "linear extrapolation in cells"
+              % (ref.source, n_fit, iters, t_fit, n_iter_target or iters, n_eval, t["jacobian"], t["divergence"],
+                 t["acceleration"], t["curvature"]))
+    return 1.0 / per_cell, sample, {"iterations_sample": iters, "iterations_target": n_iter_target or iters,
+                                    "fit_s": t_fit, **{k + "_s": v for k, v in t.items()}}
 
 
 def run_reference(a):
@@ -95,23 +185,25 @@ def run_reference(a):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    vals, sample, ms = [], "", []
+    ref = CpuReference()
+    vals, sample, ms, detail = [], "", [], {}
     for i in range(a.warmup + a.steps):
-        n_fit, n_eval = (10_000, 300) if i < a.warmup else (30_000, 1_000)
+        n_fit, n_eval = (max(2 * a.ctrl, a.ref_fit // 4), max(64, a.ref_eval // 4)) if i < a.warmup else (a.ref_fit, a.ref_eval)
         t0 = time.perf_counter()
-        rate, sample, _ = cpu_reference_rate(a, None, n_fit, n_eval)
+        rate, sample, detail = cpu_reference_rate(a, a.iters_full, n_fit, n_eval, ref)
         if i >= a.warmup:
             vals.append(rate)
             ms.append((time.perf_counter() - t0) * 1e3)
     v = float(np.mean(vals))
     line = {
-        "impl": "reference", "metric": "cells/sec for SparseVFC fit + per-cell Jacobian/divergence/acceleration/curvature",
-        "value": v, "unit": "cells/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": float(np.mean(ms)), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(a), "note": "reference algorithm (NumPy/SciPy oracle port of dynamo's "
-                   "CPU path) on the host cores; each step is a bounded sample of the workload"},
-        "cpu_baseline": {"value": v, "unit": "cells/s", "cores": cores, "kind": "port", "sample": sample},
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "cells/s", "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": float(np.mean(ms)), "higher_is_better": True, "scaling": a.scaling,
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(a), "em_iterations": a.iters_full,
+                   "note": "the reference's own CPU implementation on the host cores; each step is a bounded sample of the "
+                           "workload; the sample's fit time is RESCALED to em_iterations = the EM iteration count the "
+                           "full-size GPU job executes (the sample itself ran %d)" % detail["iterations_sample"]},
+        "cpu_baseline": {"value": v, "unit": "cells/s", "cores": cores, "kind": ref.kind, "sample": sample, **detail},
         "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -167,6 +259,72 @@ class ClockSampler:
                 "samples": len(sm), "power_w_max": max(pw) if pw else None}
 
 
+def measure_fp64_peak(device_index):
+    """FP64 peak of THIS GPU in THIS run: the DMMA / DFMA chains of tools/fp64_peak (built by build()); ~1 s."""
+    exe = os.path.join(ROOT, "tools", "fp64_peak")
+    try:
+        env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(device_index)) if "CUDA_VISIBLE_DEVICES" not in os.environ else None
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120, env=env).stdout
+        d = json.loads(out.strip().splitlines()[-1])
+        best = max(v for k, v in d.items() if k.startswith("dmma"))
+        return float(best), {k: v for k, v in d.items() if k.startswith(("dmma", "dfma"))}
+    except Exception as e:
+        return None, {"error": repr(e)}
+
+
+def rel(a_, b_):
+    a_, b_ = np.asarray(a_, dtype=np.float64), np.asarray(b_, dtype=np.float64)
+    return float(np.max(np.abs(a_ - b_)) / max(np.max(np.abs(b_)), 1e-300))
+
+
+def prefix_len(x, y, tol=1e-8):
+    n = 0
+    for p, q in zip(x, y):
+        if not abs(p - q) <= tol * abs(q):
+            break
+        n += 1
+    return n
+
+
+def parity_block(a, dvf, xs, st_vf, dev_out, n_fit=20_000):
+    """GPU against the executed reference, in the bench run itself.
+    (1) fixed C: the benchmarked device outputs (J, div, acc, curv of the timed full-size job) on a sample of its cells
+        against the reference's functions evaluated with the SAME fitted field;
+    (2) refit: SparseVFC of a subsample of the bench data at the bench's M by both sides + the reference's own
+        permutation floor (at the benchmark's M the normal-equations solve makes the reference
+        irreproducible, so the honest number is relV next to that floor and the leading iterations that agree)."""
+    ref = CpuReference()
+    out = {"against": ref.kind, "source": ref.source}
+    obj = ref.field_object(st_vf)
+    _, r = ref.calculus(xs, st_vf, obj)
+    f_ref = ref.vfu.vector_field_function(xs, st_vf) if ref.kind == "reference" else ref.o.field_eval(xs, st_vf)
+    out["fixed_C"] = {"cells": int(len(xs)), "of": "the timed device-resident outputs at the full size",
+                      "rel_V": rel(dev_out["v"], f_ref), "rel_J": rel(dev_out["J"], r["J"]),
+                      "rel_div": rel(dev_out["div"], r["div"]), "rel_acc": rel(dev_out["acc"], r["acc_mat"]),
+                      "rel_curv": rel(dev_out["curv"], r["curv_mat"]), "gate": 1e-8}
+    out["fixed_C"]["pass"] = bool(max(v for k, v in out["fixed_C"].items() if k.startswith("rel_")) < 1e-8)
+    Xs, Vs = bench_data(a, n_fit, seed=1)
+    kw = dict(M=a.ctrl, MaxIter=a.maxiter, ecr=a.ecr)
+    vr, _ = ref.fit(Xs, Vs, **kw)
+    perm = np.random.default_rng(99).permutation(n_fit)
+    vp, _ = ref.fit(Xs[perm], Vs[perm], **kw)
+    inv = np.argsort(perm)
+    fit = {"cells": n_fit, "M": a.ctrl, "iterations_reference": int(vr["iteration"]) + 1,
+           "iterations_reference_refit_permuted": int(vp["iteration"]) + 1,
+           "floor_rel_V": rel(vp["V"][inv], vr["V"]),
+           "floor_rel_C": rel(vp["C"], vr["C"]) if np.array_equal(vp["X_ctrl"], vr["X_ctrl"]) else None,
+           "floor_E_prefix_1e-8": prefix_len(vp["E_traj"], vr["E_traj"])}
+    for method in ("drouin", "cholesky"):
+        vg = dvf.SvcVectorField(Xs, Vs, None, normalize=False, **kw).train(lstsq_method=method)
+        fit[method] = {"iterations": int(vg["iteration"]) + 1, "ctrl_equal": bool(np.array_equal(vg["X_ctrl"], vr["X_ctrl"])),
+                       "rel_V": rel(vg["V"], vr["V"]), "rel_C": rel(vg["C"], vr["C"]),
+                       "E_prefix_1e-8": prefix_len(vg["E_traj"], vr["E_traj"]),
+                       "rel_E_first_iterations": [float(abs(p - q) / abs(q)) for p, q in
+                                                  list(zip(vg["E_traj"], vr["E_traj"]))[:4]]}
+    out["refit_subsample"] = fit
+    return out
+
+
 # ----------------------------------------------------------------------------------------------------------
 def run_ours(a):
     import torch
@@ -174,9 +332,8 @@ def run_ours(a):
 
     import dynamo_release_b200 as dvf
     from dynamo_release_b200 import _lib, kernels, prelude
-    from dynamo_release_b200.datasets import hematopoiesis_like
     from dynamo_release_b200.device import pinned_like
-    from dynamo_release_b200.sparsevfc import fit_em
+    from dynamo_release_b200.sparsevfc import fit_em, solver_code
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -184,14 +341,22 @@ def run_ours(a):
     comm = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        from dynamo_release_b200.dist import Comm, fit_sharded
-        comm = Comm()
+        from dynamo_release_b200.dist import default_comm, fit_sharded, shard_bounds
+        comm = default_comm()
     lib = _lib.load()
-    N, D, M = a.cells, a.pcs, a.ctrl
-    Xh, Vh = hematopoiesis_like(N, D, seed=100 + rank, velocity_scale=a.velocity_scale, manifold_seed=7)
+    D, M = a.pcs, a.ctrl
+    if a.scaling == "strong" and world > 1:
+        lo, hi = shard_bounds(a.cells, world, rank)
+        N, n_tot = hi - lo, a.cells
+    else:
+        N, n_tot = a.cells, a.cells * world
+    # FP64 peak of this GPU, measured before the timed region (rank 0)
+    peak, peak_detail = (measure_fp64_peak(local) if rank == 0 else (None, {}))
+    Xh, Vh = bench_data(a, N, seed=100 + rank)
     Xh, Vh = pinned_like(Xh), pinned_like(Vh)
     Xd, Vd = torch.from_numpy(Xh).cuda(), torch.from_numpy(Vh).cuda()
-    em = dict(MaxIter=a.maxiter)
+    solver = solver_code(a.lstsq)
+    em = dict(MaxIter=a.maxiter, ecr=a.ecr, solver=solver)
     J_buf = torch.empty((D, D, N), dtype=torch.float64, device="cuda")
     state = {}
 
@@ -224,13 +389,15 @@ def run_ours(a):
         r = kernels.div_acc_curv(Xd, ctrl, beta, st.C, formula=2)
         ev.append(mark())
         stage_ev.append(ev)
-        state.update(n_iter=st.n_iter, sigma2=st.sigma2, n_inlier=st.n_inlier, r=r)
+        state.update(n_iter=st.n_iter, sigma2=st.sigma2, n_inlier=st.n_inlier, r=r, st=st, ctrl=ctrl, beta=beta)
 
     def step_e2e():
-        """public numpy API: pinned host arrays in, numpy arrays out (single GPU path of the drop-in)"""
+        """public numpy API: pinned host arrays in, numpy arrays out.  N > 1: one joint sharded fit (every rank passes
+        its row block and keeps the results of its rows), evaluation of the rank's own cells."""
         t = [time.perf_counter()]
-        vfc = dvf.SvcVectorField(Xh, Vh, None, normalize=False, M=M, **em)
-        vf = vfc.train()
+        kw = dict(sharded=True, gather=False) if world > 1 else {}
+        vfc = dvf.SvcVectorField(Xh, Vh, None, normalize=False, M=M, MaxIter=a.maxiter, ecr=a.ecr, **kw)
+        vf = vfc.train(lstsq_method=a.lstsq)
         t.append(time.perf_counter())
         J = dvf.Jacobian_rkhs_gaussian(Xh, vf)
         t.append(time.perf_counter())
@@ -245,6 +412,7 @@ def run_ours(a):
         h2d = 6 * Xh.nbytes                                 # X, V for the fit + X for each of the 4 evaluations
         d2h = (vf["V"].nbytes + vf["P"].nbytes + vf["C"].nbytes + J.nbytes + div.nbytes + acc.nbytes +
                acc_mat.nbytes + curv.nbytes + curv_mat.nbytes)
+        state["e2e_jacobian_bytes"] = J.nbytes
         return h2d, d2h
 
     # ---- device-resident timing ----
@@ -271,9 +439,27 @@ def run_ours(a):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    value = world * N / (ms * 1e-3)
+    value = n_tot / (ms * 1e-3)
 
-    # ---- end-to-end through the numpy API (rank-local job; with N ranks, N independent API calls) ----
+    # ---- parity of the benchmarked outputs (rank 0, single GPU) + sharded-vs-single parity (N > 1) ----
+    parity = None
+    if rank == 0 and world == 1 and not a.no_parity:
+        st = state["st"]
+        vf_fit = {"X_ctrl": np.asarray(state["ctrl"]), "beta": state["beta"], "C": st.C.cpu().numpy()}
+        r = state["r"]
+        cells = np.unique(np.linspace(0, N - 1, 192).astype(np.int64))
+        sel = torch.as_tensor(cells, device="cuda")
+        dev_out = {k: r[k][sel].cpu().numpy() for k in ("v", "div", "acc", "curv")}   # the sampled cells only
+        dev_out["J"] = J_buf[:, :, sel].cpu().numpy()
+        try:
+            parity = parity_block(a, dvf, np.ascontiguousarray(Xh[cells]), vf_fit, dev_out, n_fit=min(20_000, N))
+        except Exception as e:   # the bench line must not be lost to a checker problem; say so instead
+            parity = {"error": repr(e)}
+    parity_vs_1gpu = None
+    if world > 1 and not a.no_parity:
+        parity_vs_1gpu = sharded_parity(a, dvf, comm, rank, world)
+
+    # ---- end-to-end through the numpy API ----
     e2e = None
     if not a.no_e2e:
         for _ in range(max(1, min(a.warmup, 2))):
@@ -287,26 +473,32 @@ def run_ours(a):
         t = torch.tensor([dt], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * N / float(t.item()), "unit": "cells/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": float(t.item()) * 1e3,
-               "stages_ms_last_step": state.get("e2e_stages_ms"),
-               "note": "numpy API, pinned host inputs, numpy outputs incl. the %.1f GB Jacobian; N>1: one API job "
-                       "per rank" % (J_buf.numel() * 8 / 1e9)}
+        e2e = {"value": n_tot / float(t.item()), "unit": "cells/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "d2h_jacobian_bytes_per_step": int(state["e2e_jacobian_bytes"]),
+               "ms_per_step": float(t.item()) * 1e3, "stages_ms_last_step": state.get("e2e_stages_ms"),
+               "note": "numpy API, pinned host inputs, numpy outputs incl. the %.1f GB Jacobian; bytes are per rank; "
+                       "N>1: ONE joint fit through SvcVectorField(..., sharded=True), every rank moves its own shard"
+                       % (J_buf.numel() * 8 / 1e9)}
 
     if rank == 0:
         n_iter = state["n_iter"]
-        n_tot = world * N
         # algorithmic flops of one Gram launch: symmetric Gram M^2 + M, RHS 2 M D per cell
         gram_flops = float(N) * (M * M + M + 2.0 * M * D)
         per_launch_ms = gram_ms.value / max(1, a.steps * n_iter)   # launches after the stop flag return at once
         achieved = gram_flops / (per_launch_ms * 1e-3) / 1e12 if per_launch_ms > 0 else 0.0
+        peak_used = peak if peak else FP64_PEAK_FALLBACK
+        # whole step by SURVEY 8d's count (per GPU): T N F_fit + N (F_J + F_dac)
+        F_fit = M * M + 9 * M * D + 3 * M + 6 * D
+        F_J = 2 * M * D * D + 4 * M * D + M + D * D
+        F_dac = 12 * M * D + M + 8 * D
+        W_step = float(N) * (n_iter * F_fit + F_J + F_dac)
+        step_tf = W_step / (ms * 1e-3) / 1e12
         line = {
-            "metric": "cells/sec for SparseVFC fit + per-cell Jacobian/divergence/acceleration/curvature",
-            "value": value, "unit": "cells/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "metric": METRIC, "value": value, "unit": "cells/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": a.scaling, "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": workload_name(a), "cells_total": n_tot, "em_iterations": n_iter,
-                       "sigma2": state["sigma2"], "inlier_frac": state["n_inlier"] / n_tot,
+            "config": {"workload": workload_name(a), "cells_total": n_tot, "cells_per_gpu": N, "em_iterations": n_iter,
+                       "lstsq_method": a.lstsq, "sigma2": state["sigma2"], "inlier_frac": state["n_inlier"] / n_tot,
                        "l2": "inputs larger than L2 (UY %.1f GB, J %.1f GB per GPU)"
                              % (N * kernels.row_width(M, D) * 8 / 1e9, J_buf.numel() * 8 / 1e9),
                        "parallelism": "cells sharded over %d GPU(s); Gram/RHS allreduce per EM iteration" % world},
@@ -314,30 +506,83 @@ def run_ours(a):
             "stages_ms": {k: float(np.mean([ev[i].elapsed_time(ev[i + 1]) for ev in stage_ev]))
                           for i, k in enumerate(["prelude", "fit", "jacobian", "div_acc_curv"])},
             "e2e": e2e,
+            "parity": parity,
             "gpu_launches": int(launches.value),
             "roofline": {"bound": "tensor", "kernel": "k_gram_parts (k_gram for many tiles): weighted Gram + RHS, FP64 DMMA m8n8k4 fed by TMA, + its reduce kernel",
-                         "achieved": achieved, "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s",
-                         "frac": achieved / FP64_PEAK_TFLOPS,
+                         "achieved": achieved, "peak": peak_used, "unit": "TFLOP/s",
+                         "frac": achieved / peak_used,
+                         "peak_measured_in_run": peak, "peak_detail": peak_detail,
+                         "peak_source": "FP64 DMMA m8n8k4 / m16n8k16 chains of tools/fp64_peak run on this GPU before the "
+                                        "timed region (MEASURED_PEAKS.json has no FP64 entry; round-1 constant 37.1, "
+                                        "cuBLAS DGEMM 35.5)" if peak else "fallback constant (tools/fp64_peak did not run)",
                          # dram__bytes_read.sum + dram__bytes_write.sum of one k_gram launch at the default workload from
-                         # the committed ncu --set full capture (profiles/ncu_k_gram_r01_details.txt); null elsewhere
+                         # the committed ncu --set full capture; null elsewhere
                          "traffic": GRAM_DRAM_BYTES_NCU if (N, D, M) == (1_000_000, 30, 500) else None,
                          "traffic_unit": "bytes per launch (compulsory: %d)" % (N * kernels.row_width(M, D) * 8),
                          "ms_per_launch": per_launch_ms, "launches_timed": a.steps * n_iter,
                          "share_of_step": gram_ms.value / a.steps / ms,
-                         "peak_source": "FP64 DMMA peak measured on this pool (tools/fp64_peak.cu: 37.1 TFLOP/s; "
-                                        "cuBLAS DGEMM 35.5); MEASURED_PEAKS.json has no FP64 entry",
                          "algorithmic_flops_per_launch": gram_flops,
                          "hbm_GBps_compulsory": N * kernels.row_width(M, D) * 8 / (per_launch_ms * 1e-3) / 1e9
-                         if per_launch_ms > 0 else None},
+                         if per_launch_ms > 0 else None,
+                         "step": {"flops": W_step, "achieved": step_tf, "frac": step_tf / peak_used,
+                                  "note": "SURVEY 8d: T N (M^2+9MD+3M+6D) + N (F_J + F_dac) per GPU over the device-resident "
+                                          "step; credits 3MD+M per cell and iteration (kernel re-evaluation) that this "
+                                          "build does not execute because it keeps U in HBM"}},
         }
+        if parity_vs_1gpu is not None:
+            line["parity_vs_1gpu"] = parity_vs_1gpu
         if not a.no_cpu_baseline and world == 1:
-            rate, sample, _ = cpu_reference_rate(a, n_iter)
-            line["cpu_baseline"] = {"value": rate, "unit": "cells/s", "cores": os.cpu_count(), "kind": "port",
-                                    "sample": sample}
+            ref = CpuReference()
+            rate, sample, detail = cpu_reference_rate(a, n_iter, a.ref_fit, a.ref_eval, ref)
+            line["cpu_baseline"] = {"value": rate, "unit": "cells/s", "cores": os.cpu_count(), "kind": ref.kind,
+                                    "sample": sample, **detail}
+            if ref.kind == "reference":   # cross-check: the NumPy port on the same sample
+                prate, _, _ = cpu_reference_rate(a, n_iter, a.ref_fit, a.ref_eval, CpuReference(force_port=True))
+                line["cpu_baseline"]["port_cross_check_cells_per_s"] = prate
         print(json.dumps(line), flush=True)
     if world > 1:
-        comm.close()
+        from dynamo_release_b200.dist import close_default_comm
+        close_default_comm()
         dist.destroy_process_group()
+
+
+def sharded_parity(a, dvf, comm, rank, world, n_total=200_000):
+    """The sharded fit against the single-GPU fit of the SAME data, on a reduced size inside the bench run: bench-shaped
+    data at the bench's M with both solvers (the normal-equations default amplifies the different summation order of
+    the sharded Gram by cond^2 -- see parity.refit_subsample's floor -- Cholesky by cond), plus a well-conditioned
+    control (velocity_scale 1) that must agree to 1e-10."""
+    import torch
+    import torch.distributed as dist
+    from dynamo_release_b200 import prelude
+    from dynamo_release_b200.datasets import hematopoiesis_like
+    from dynamo_release_b200.dist import fit_sharded, shard_bounds
+    from dynamo_release_b200.sparsevfc import fit_em, solver_code
+
+    out = {}
+    cases = [("bench_shaped", a.velocity_scale, a.ctrl), ("well_conditioned", 1.0, min(a.ctrl, 100))]
+    for tag, vs, m in cases:
+        X, V = hematopoiesis_like(n_total, a.pcs, seed=9, velocity_scale=vs, manifold_seed=7)
+        lo, hi = shard_bounds(n_total, world, rank)
+        for method in ("drouin", "cholesky"):
+            kw = dict(MaxIter=min(a.maxiter, 12), ecr=a.ecr, solver=solver_code(method))
+            st, ctrl, idx, beta, _ = fit_sharded(X[lo:hi], V[lo:hi], m, comm, **kw)
+            if rank == 0:
+                Xd, Vd = torch.from_numpy(X).cuda(), torch.from_numpy(V).cuda()
+                _, Xv, Yv, ctrl1, idx1, beta1 = prelude.run(Xd, Vd, m)
+                s1 = fit_em(Xv, Yv, ctrl1, beta1, **kw)
+                nloc = st.V.shape[0]
+                out["%s/%s" % (tag, method)] = {
+                    "cells": n_total, "M": m, "iterations": [st.n_iter, s1.n_iter],
+                    "ctrl_equal": bool(np.array_equal(idx, idx1) and np.array_equal(ctrl.cpu().numpy(), ctrl1) and beta == beta1),
+                    "rel_C": float((st.C - s1.C).abs().max() / s1.C.abs().max()),
+                    "rel_V": float((st.V - s1.V[:nloc]).abs().max() / s1.V.abs().max()),
+                    "rel_sigma2": abs(st.sigma2 - s1.sigma2) / abs(s1.sigma2)}
+            dist.barrier()
+    if rank == 0:
+        wc = out["well_conditioned/cholesky"]
+        out["pass"] = bool(wc["ctrl_equal"] and wc["iterations"][0] == wc["iterations"][1] and wc["rel_C"] < 1e-10
+                           and wc["rel_V"] < 1e-10 and out["bench_shaped/cholesky"]["ctrl_equal"])
+    return out if rank == 0 else None
 
 
 if __name__ == "__main__":

@@ -10,6 +10,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("DVF_LIB_PATH") or os.path.join(_HERE, "libdvf_b200.so")  # env: developer experiments
 
+SOLVER_CHOLESKY, SOLVER_NORMAL_LU = 0, 1   # DVF_SOLVER_* of include/dvf_b200.h
 DVF_OK, DVF_ERR_ARG, DVF_ERR_CUDA, DVF_ERR_NUMERIC, DVF_ERR_COMM, DVF_ERR_WORKSPACE = 0, -1, -2, -3, -4, -5
 
 
@@ -23,7 +24,8 @@ class DvfError(RuntimeError):
 
 class EmParams(C.Structure):  # dvf_em_params
     _fields_ = [("a", C.c_double), ("gamma", C.c_double), ("lambda_", C.c_double), ("minP", C.c_double),
-                ("ecr", C.c_double), ("theta", C.c_double), ("max_iter", C.c_int), ("check_every", C.c_int)]
+                ("ecr", C.c_double), ("theta", C.c_double), ("max_iter", C.c_int), ("check_every", C.c_int),
+                ("solver", C.c_int), ("reserved", C.c_int)]
 
 
 class EmResult(C.Structure):  # dvf_em_result
@@ -70,6 +72,8 @@ SIGNATURES = {
     "dvf_gram_scratch_bytes": (_i, [_i64, _i, _i, C.POINTER(_sz)]),
     "dvf_gram": (_i, [_p, _p, _d, _i64, _i, _i, _p, _p, _sz, _p]),
     "dvf_solve": (_i, [_p, _i64, _p, _i, _i, _d, _p, _p, _p, _p]),
+    "dvf_solve_normal_workspace_bytes": (_i, [_i, _i, C.POINTER(_sz)]),
+    "dvf_solve_normal": (_i, [_p, _i64, _p, _i, _i, _d, _p, _sz, _p, _p, _p]),
     "dvf_update_v": (_i, [_p, _p, _p, _d, _i64, _i, _i, _p, _p, _p, _p]),
     "dvf_comm_unique_id": (_i, [_p]),
     "dvf_comm_init": (_i, [_p, _i, _i, C.POINTER(_p)]),

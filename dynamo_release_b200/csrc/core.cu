@@ -245,5 +245,5 @@ extern "C" int dvf_memcpy2d_async(void* dst, size_t dpitch, const void* src, siz
     return DVF_OK;
 }
 
-extern "C" int dvf_abi_version(void) { return 1; }
+extern "C" int dvf_abi_version(void) { return 2; }
 extern "C" const char* dvf_last_error(void) { return dvf::g_err; }

@@ -28,6 +28,11 @@ int gram_run(const gram_plan& pl, const double* UY, const double* P, int64_t N, 
 int solve_run(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
               const double* lam_sigma2_ptr, double* L, double* C, int* info, const int* done, cudaStream_t st);
 
+// the reference's solver form: normal equations + LU with partial pivoting (kern_solve.cu, k_lu_solve)
+size_t solve_normal_ws_bytes(int M, int D);
+int solve_normal_run(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
+                     const double* lam_sigma2_ptr, void* ws, double* C, int* info, const int* done, cudaStream_t st);
+
 constexpr int ES_THREADS = 256;
 constexpr int ES_MAX_BLOCKS = 1184;   // 8 per SM on 148 SMs; fixed => partial-sum order is reproducible
 inline int estep_blocks(int64_t N) {

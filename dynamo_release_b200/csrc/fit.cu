@@ -29,7 +29,10 @@ static fit_layout make_layout(int64_t N, int D, int M) {
     l.r2 = o;       o += al(sizeof(double) * (size_t)(N + 2));
     l.gbuf = o;     o += al(sizeof(double) * ((size_t)l.ldg * l.ldg + RED_COUNT));
     l.gscratch = o; o += al(l.gp.scratch_bytes);
-    l.L = o;        o += al(sizeof(double) * (size_t)(M + D) * M);
+    {
+        size_t chol = sizeof(double) * (size_t)(M + D) * M, lu = solve_normal_ws_bytes(M, D);
+        l.L = o;    o += al(chol > lu ? chol : lu);
+    }
     l.Kc = o;       o += al(sizeof(double) * (size_t)M * M);
     l.Cp = o;       o += al(sizeof(double) * (size_t)l.Mp * l.DP);
     size_t np = (size_t)l.nblk_es * 4;
@@ -130,6 +133,7 @@ extern "C" int dvf_fit_em(const double* X, const double* Y, int64_t N, int64_t N
     DVF_ARG(N >= 1 && N_total >= N && M >= 1, "bad shape N=%lld N_total=%lld M=%d", (long long)N, (long long)N_total, M);
     DVF_ARG(D >= 1 && D <= kMaxD, "D=%d unsupported (1..%d)", D, kMaxD);
     DVF_ARG(prm->max_iter >= 0, "max_iter < 0");
+    DVF_ARG(prm->solver == DVF_SOLVER_CHOLESKY || prm->solver == DVF_SOLVER_NORMAL_LU, "unknown solver %d", prm->solver);
     const fit_layout l = make_layout(N, D, M);
     if (ws_bytes < l.total) {
         set_error("fit workspace too small: %zu < %zu", ws_bytes, l.total);
@@ -185,7 +189,11 @@ extern "C" int dvf_fit_em(const double* X, const double* Y, int64_t N, int64_t N
         k_ctl_energy<<<1, 1, 0, st>>>(ctl, red, part, prm->lambda_, D, E_traj, tecr_traj);
         DVF_LAUNCH_CHECK();
         // ---- solve (:481), V = U C and sigma2 / gamma (:484-495) ----
-        if (int rc = solve_run(G, l.ldg, Kc, M, D, 0.0, &ctl->lam_sigma2, Lw, C, &ctl->info, done, st)) return rc;
+        if (prm->solver == DVF_SOLVER_NORMAL_LU) {
+            if (int rc = solve_normal_run(G, l.ldg, Kc, M, D, 0.0, &ctl->lam_sigma2, Lw, C, &ctl->info, done, st)) return rc;
+        } else {
+            if (int rc = solve_run(G, l.ldg, Kc, M, D, 0.0, &ctl->lam_sigma2, Lw, C, &ctl->info, done, st)) return rc;
+        }
         if (int rc = pad_c_run(C, M, D, Cp, l.Mp, l.DP, done, st)) return rc;
         if (int rc = update_v_run(UY, Cp, P, prm->minP, N, D, M, V, r2, part, done, st)) return rc;
         if (int rc = sum_partials_run(part, (int)l.nblk_uv, 1, scal + 2, done, st)) return rc;
@@ -213,8 +221,11 @@ extern "C" int dvf_fit_em(const double* X, const double* Y, int64_t N, int64_t N
     res->status = 0;
     if (h.info != 0) {
         res->status = DVF_ERR_NUMERIC;
-        set_error("Cholesky met a non-positive pivot at column %d in EM iteration %d (lhs not positive definite)",
-                  h.info - 1, h.iter);
+        if (prm->solver == DVF_SOLVER_NORMAL_LU)
+            set_error("Singular matrix: LU of lhs^T lhs met a zero pivot at column %d in EM iteration %d", h.info - 1, h.iter);
+        else
+            set_error("Cholesky met a non-positive pivot at column %d in EM iteration %d (lhs not positive definite)",
+                      h.info - 1, h.iter);
         return DVF_ERR_NUMERIC;
     }
     return DVF_OK;

@@ -203,3 +203,330 @@ extern "C" int dvf_solve(const double* G, int64_t ldg, const double* Kc, int M, 
     DVF_CUDA(cudaMemsetAsync(info, 0, sizeof(int), (cudaStream_t)stream));
     return solve_run(G, ldg, Kc, M, D, lam_sigma2, nullptr, L, C, info, nullptr, (cudaStream_t)stream);
 }
+
+namespace dvf {
+
+// =========================================================================================================
+// K4': the reference's own solver form (lstsq_method="drouin"): tools/utils.py:2975-2976
+//     i = dgemm(a.T, a.T, trans_b=True)          ->  N = lhs^T lhs
+//     x = np.linalg.solve(i, dgemm(a.T, b))      ->  LAPACK gesv: LU with partial pivoting of N, then the two
+//                                                    triangular solves applied to lhs^T rhs
+// One cooperative launch.  lhs is symmetric (lower triangle of the Gram mirrored + lambda sigma2 Kc), so
+// lhs^T [lhs | rhs] = lhs [lhs | rhs]: phase 1 is one tiled product into the augmented matrix N = [lhs^T lhs | lhs^T rhs]
+// (M x (M + D)); the right-hand sides ride along as extra columns, so the forward substitution of gesv happens during
+// the elimination.  LU: right-looking, panels of LU_NB columns; the panel is factored by CTA 0 with one matrix row per
+// thread held in registers (pivot = first entry of largest magnitude, LAPACK's idamax rule; row exchange through shared
+// memory), the other CTAs join for the row swaps + U12 = L11^-1 N12 and for the trailing update.  The back
+// substitution runs in CTA 0.  Squares cond(lhs) exactly as the reference does -- that is the point of this path.
+// =========================================================================================================
+constexpr int LU_NB = 16;
+constexpr int LU_THREADS = 1024;
+constexpr int LU_TR = 64, LU_TC = 128;   // tile of the product kernels: 64 rows x 128 columns, 2 x 4 outputs per thread
+
+struct lu_args {
+    const double* G; int64_t ldg; const double* Kc; int M; int D;
+    double lam_sigma2; const double* lam_sigma2_ptr;
+    double* AB; double* N; int ldn; int* piv; double* C; int* info; const int* done;
+};
+
+// Cd[i][j] (rows x cols, ld ldc) = (acc ? Cd : 0) + sign * sum_{c<K} P[i][c] Q[c][j], tiles dealt round-robin to the CTAs
+__device__ void lu_tile_product(double* Cd, int ldc, const double* P, int ldp, const double* Q, int ldq, int rows,
+                                int cols, int K, double sign, bool acc, double (*Ps)[LU_NB + 1], double (*Qs)[LU_TC]) {
+    const int tid = threadIdx.x;
+    const int ntr = (rows + LU_TR - 1) / LU_TR, ntc = (cols + LU_TC - 1) / LU_TC;
+    const int ty = tid >> 5, tx = tid & 31;      // 32 x 32 threads: rows ty, ty + 32; columns tx + 32 v
+    for (int tile = blockIdx.x; tile < ntr * ntc; tile += gridDim.x) {
+        const int i0 = (tile / ntc) * LU_TR, j0 = (tile % ntc) * LU_TC;
+        double s[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+        for (int c0 = 0; c0 < K; c0 += LU_NB) {
+            __syncthreads();
+            {   // P tile: 64 x 16 = 1024 entries, one per thread
+                const int r = tid >> 4, c = tid & 15;
+                Ps[r][c] = (i0 + r < rows && c0 + c < K) ? P[(int64_t)(i0 + r) * ldp + c0 + c] : 0.0;
+            }
+            for (int e = tid; e < LU_NB * LU_TC; e += LU_THREADS) {
+                const int c = e / LU_TC, j = e % LU_TC;
+                Qs[c][j] = (c0 + c < K && j0 + j < cols) ? Q[(int64_t)(c0 + c) * ldq + j0 + j] : 0.0;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int c = 0; c < LU_NB; ++c) {
+                const double p0 = Ps[ty][c], p1 = Ps[ty + 32][c];
+#pragma unroll
+                for (int v = 0; v < 4; ++v) {
+                    const double q = Qs[c][tx + 32 * v];
+                    s[0][v] = fma(p0, q, s[0][v]);
+                    s[1][v] = fma(p1, q, s[1][v]);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+                const int i = i0 + ty + 32 * u, j = j0 + tx + 32 * v;
+                if (i < rows && j < cols) {
+                    double* dst = Cd + (int64_t)i * ldc + j;
+                    *dst = acc ? fma(sign, s[u][v], *dst) : sign * s[u][v];
+                }
+            }
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(LU_THREADS) k_lu_solve(lu_args a) {
+    cg::grid_group grid = cg::this_grid();
+    if (a.done && *a.done) return;
+    __shared__ double Ps[LU_TR][LU_NB + 1];
+    __shared__ double Qs[LU_NB][LU_TC];
+    __shared__ double rowP[LU_NB], rowJ[LU_NB];
+    __shared__ double wval[32];
+    __shared__ int widx[32];
+    __shared__ int s_piv;
+    const int M = a.M, D = a.D, W = a.M + a.D, ldn = a.ldn;
+    const int tid = threadIdx.x;
+    const int64_t gtid = (int64_t)blockIdx.x * LU_THREADS + tid, gsz = (int64_t)gridDim.x * LU_THREADS;
+    const double ls = a.lam_sigma2_ptr ? *a.lam_sigma2_ptr : a.lam_sigma2;
+    double* AB = a.AB;
+    double* N = a.N;
+
+    // phase 0: AB = [lhs | rhs], lhs symmetric from the lower triangle of G
+    for (int64_t e = gtid; e < (int64_t)M * W; e += gsz) {
+        const int i = (int)(e / W), j = (int)(e % W);
+        double v;
+        if (j >= M) v = a.G[(int64_t)j * a.ldg + i];                       // rhs[i][d] = G[M + d][i]
+        else {
+            const int hi = i > j ? i : j, lo = i > j ? j : i;
+            v = a.G[(int64_t)hi * a.ldg + lo] + ls * a.Kc[(int64_t)i * M + j];
+        }
+        AB[(int64_t)i * ldn + j] = v;
+    }
+    grid.sync();
+    // phase 1: N = lhs [lhs | rhs]
+    lu_tile_product(N, ldn, AB, ldn, AB, ldn, M, W, M, 1.0, false, Ps, Qs);
+    grid.sync();
+
+    // phase 2: LU with partial pivoting
+    for (int k0 = 0; k0 < M; k0 += LU_NB) {
+        const int nbe = min(LU_NB, M - k0);
+        if (blockIdx.x == 0) {
+            double av[R][LU_NB];
+#pragma unroll
+            for (int q = 0; q < R; ++q) {
+                const int r = k0 + tid + LU_THREADS * q;
+#pragma unroll
+                for (int c = 0; c < LU_NB; ++c) av[q][c] = (r < M && c < nbe) ? N[(int64_t)r * ldn + k0 + c] : 0.0;
+            }
+#pragma unroll
+            for (int j = 0; j < LU_NB; ++j) {
+                if (j < nbe) {                     // uniform over the CTA
+                    // pivot: first row >= k0 + j with the largest |entry| in column j
+                    double bv = -1.0;
+                    int bi = 0x7fffffff;
+#pragma unroll
+                    for (int q = 0; q < R; ++q) {
+                        const int r = k0 + tid + LU_THREADS * q;
+                        const double v = fabs(av[q][j]);
+                        if (r < M && r >= k0 + j && (v > bv)) { bv = v; bi = r; }
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                        if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+                    }
+                    if ((tid & 31) == 0) { wval[tid >> 5] = bv; widx[tid >> 5] = bi; }
+                    __syncthreads();
+                    if (tid < 32) {
+                        bv = wval[tid]; bi = widx[tid];
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+                        }
+                        if (tid == 0) {
+                            s_piv = bi;
+                            a.piv[j] = bi;
+                            if (!(bv > 0.0)) atomicCAS(a.info, 0, k0 + j + 1);      // exactly singular (or NaN)
+                        }
+                    }
+                    __syncthreads();
+                    const int p = s_piv;
+#pragma unroll
+                    for (int q = 0; q < R; ++q) {
+                        const int r = k0 + tid + LU_THREADS * q;
+                        if (r == p) {
+#pragma unroll
+                            for (int c = 0; c < LU_NB; ++c) rowP[c] = av[q][c];
+                        }
+                        if (r == k0 + j) {
+#pragma unroll
+                            for (int c = 0; c < LU_NB; ++c) rowJ[c] = av[q][c];
+                        }
+                    }
+                    __syncthreads();
+                    const double pv = rowP[j];
+#pragma unroll
+                    for (int q = 0; q < R; ++q) {
+                        const int r = k0 + tid + LU_THREADS * q;
+                        if (r == k0 + j) {
+#pragma unroll
+                            for (int c = 0; c < LU_NB; ++c) av[q][c] = rowP[c];
+                        } else if (r == p) {
+#pragma unroll
+                            for (int c = 0; c < LU_NB; ++c) av[q][c] = rowJ[c];
+                        }
+                        if (r > k0 + j && r < M) {
+                            const double l = av[q][j] / pv;
+                            av[q][j] = l;
+#pragma unroll
+                            for (int c = 0; c < LU_NB; ++c)
+                                if (c > j) av[q][c] = fma(-l, rowP[c], av[q][c]);
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < R; ++q) {
+                const int r = k0 + tid + LU_THREADS * q;
+                if (r < M) {
+#pragma unroll
+                    for (int c = 0; c < LU_NB; ++c)
+                        if (c < nbe) N[(int64_t)r * ldn + k0 + c] = av[q][c];
+                }
+            }
+        }
+        grid.sync();
+        // row swaps of the columns to the right of the panel (incl. the right-hand sides), then U12 = L11^-1 N12
+        {
+            double (*L11)[LU_NB + 1] = Ps;
+            if (tid < LU_NB * LU_NB) {
+                const int i = tid / LU_NB, j = tid % LU_NB;
+                L11[i][j] = (i < nbe && j < i) ? N[(int64_t)(k0 + i) * ldn + k0 + j] : 0.0;
+            }
+            __syncthreads();
+            for (int64_t cc = k0 + nbe + gtid; cc < W; cc += gsz) {
+                double u[LU_NB];
+#pragma unroll
+                for (int j = 0; j < LU_NB; ++j) {
+                    if (j < nbe) {
+                        const int p = a.piv[j];
+                        double* x = N + (int64_t)(k0 + j) * ldn + cc;
+                        if (p != k0 + j) {
+                            double* y = N + (int64_t)p * ldn + cc;
+                            const double t = *x; *x = *y; *y = t;
+                        }
+                        double s = *x;
+#pragma unroll
+                        for (int i = 0; i < LU_NB; ++i)
+                            if (i < j) s = fma(-L11[j][i], u[i], s);
+                        u[j] = s;
+                        *x = s;
+                    }
+                }
+            }
+        }
+        grid.sync();
+        // trailing update N22 -= L21 U12
+        const int r0 = k0 + nbe;
+        if (r0 < M)
+            lu_tile_product(N + (int64_t)r0 * ldn + r0, ldn, N + (int64_t)r0 * ldn + k0, ldn, N + (int64_t)k0 * ldn + r0, ldn,
+                            M - r0, W - r0, nbe, -1.0, true, Ps, Qs);
+        grid.sync();
+    }
+
+    // phase 3: back substitution U X = Y (Y = columns M .. M+D-1 of N), CTA 0
+    if (blockIdx.x != 0) return;
+    double (*Ub)[LU_NB + 1] = Ps;                   // U block, 16 x 16
+    double (*Xb)[LU_TC] = Qs;                       // solved block rows, 16 x D   (D <= 64 < LU_TC)
+    const int nblk = (M + LU_NB - 1) / LU_NB;
+    for (int kb = nblk - 1; kb >= 0; --kb) {
+        const int k0 = kb * LU_NB, nbe = min(LU_NB, M - k0);
+        __syncthreads();
+        if (tid < LU_NB * LU_NB) {
+            const int i = tid / LU_NB, j = tid % LU_NB;
+            Ub[i][j] = (i < nbe && j < nbe && j >= i) ? N[(int64_t)(k0 + i) * ldn + k0 + j] : (i == j ? 1.0 : 0.0);
+        }
+        for (int e = tid; e < LU_NB * D; e += LU_THREADS) {
+            const int i = e / D, d = e % D;
+            Xb[i][d] = (i < nbe) ? N[(int64_t)(k0 + i) * ldn + M + d] : 0.0;
+        }
+        __syncthreads();
+        if (tid < D) {
+            for (int i = nbe - 1; i >= 0; --i) {
+                double s = Xb[i][tid];
+                for (int j = i + 1; j < nbe; ++j) s = fma(-Ub[i][j], Xb[j][tid], s);
+                Xb[i][tid] = s / Ub[i][i];
+            }
+        }
+        __syncthreads();
+        for (int e = tid; e < nbe * D; e += LU_THREADS) a.C[(int64_t)(k0 + e / D) * D + e % D] = Xb[e / D][e % D];
+        for (int e = tid; e < k0 * D; e += LU_THREADS) {
+            const int i = e / D, d = e % D;
+            double s = N[(int64_t)i * ldn + M + d];
+            const double* urow = N + (int64_t)i * ldn + k0;
+            for (int j = 0; j < nbe; ++j) s = fma(-urow[j], Xb[j][d], s);
+            N[(int64_t)i * ldn + M + d] = s;
+        }
+    }
+}
+
+static inline int lu_ldn(int M, int D) { return (M + D + 1) & ~1; }
+
+size_t solve_normal_ws_bytes(int M, int D) {
+    return sizeof(double) * 2 * (size_t)M * lu_ldn(M, D) + 256;
+}
+
+int solve_normal_run(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
+                     const double* lam_sigma2_ptr, void* ws, double* C, int* info, const int* done, cudaStream_t st) {
+    if (M > 4 * LU_THREADS) {
+        set_error("lstsq_method='drouin' (normal equations + LU) supports M <= %d control points; M = %d", 4 * LU_THREADS, M);
+        return DVF_ERR_ARG;
+    }
+    const int ldn = lu_ldn(M, D);
+    double* AB = (double*)ws;
+    double* N = AB + (size_t)M * ldn;
+    int* piv = (int*)(N + (size_t)M * ldn);
+    lu_args a{G, ldg, Kc, M, D, lam_sigma2, lam_sigma2_ptr, AB, N, ldn, piv, C, info, done};
+    const void* fn = M <= LU_THREADS ? (const void*)k_lu_solve<1>
+                     : (M <= 2 * LU_THREADS ? (const void*)k_lu_solve<2> : (const void*)k_lu_solve<4>);
+    static int resident[3] = {-1, -1, -1};
+    const int slot = M <= LU_THREADS ? 0 : (M <= 2 * LU_THREADS ? 1 : 2);
+    if (resident[slot] < 0) {
+        int per_sm = 0;
+        DVF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, LU_THREADS, 0));
+        resident[slot] = per_sm > 0 ? num_sms() : 0;
+    }
+    if (resident[slot] == 0) { set_error("k_lu_solve cannot be made resident"); return DVF_ERR_CUDA; }
+    int grid = ((M + LU_TR - 1) / LU_TR) * ((M + D + LU_TC - 1) / LU_TC);
+    if (grid < 8) grid = 8;
+    if (grid > resident[slot]) grid = resident[slot];
+    static const char* force = getenv("DVF_SOLVE_GRID");
+    if (force && atoi(force) > 0) grid = std::min(atoi(force), resident[slot]);
+    void* params[] = {&a};
+    ++g_launch_count;
+    DVF_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(LU_THREADS), params, 0, st));
+    return DVF_OK;
+}
+
+}  // namespace dvf
+
+extern "C" int dvf_solve_normal_workspace_bytes(int M, int D, size_t* out) {
+    DVF_ARG(out && M >= 1 && D >= 1 && D <= dvf::kMaxD, "bad argument");
+    *out = dvf::solve_normal_ws_bytes(M, D);
+    return DVF_OK;
+}
+
+extern "C" int dvf_solve_normal(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
+                                void* ws, size_t ws_bytes, double* C, int* info, void* stream) {
+    DVF_ARG(G && Kc && ws && C && info, "NULL pointer");
+    DVF_ARG(M >= 1 && D >= 1 && D <= dvf::kMaxD && ldg >= M + D, "bad shape M=%d D=%d ldg=%lld", M, D, (long long)ldg);
+    if (ws_bytes < dvf::solve_normal_ws_bytes(M, D)) {
+        dvf::set_error("normal-equations solver workspace too small");
+        return DVF_ERR_WORKSPACE;
+    }
+    DVF_CUDA(cudaMemsetAsync(info, 0, sizeof(int), (cudaStream_t)stream));
+    return dvf::solve_normal_run(G, ldg, Kc, M, D, lam_sigma2, nullptr, ws, C, info, nullptr, (cudaStream_t)stream);
+}

@@ -192,3 +192,89 @@ def integrate_sharded(init_states, t, integration_direction, f, dst=0, **kwargs)
     if rank != dst:
         return tt, Y
     return [x for p in parts for x in p[0]], [y for p in parts for y in p[1]]
+
+
+# ------------------------------------------------------------------------------------------------------
+# The sharded fit behind the drop-in names (SURVEY.md section 5 "one env var / kwarg to select the devices")
+# ------------------------------------------------------------------------------------------------------
+_COMM = None
+
+
+def default_comm() -> Comm:
+    """One NCCL communicator per process over the default torch.distributed group, created on first use."""
+    global _COMM
+    if _COMM is None or not _COMM.handle:
+        _COMM = Comm()
+    return _COMM
+
+
+def close_default_comm():
+    global _COMM
+    if _COMM is not None:
+        _COMM.close()
+        _COMM = None
+
+
+def active() -> bool:
+    """True when this process is one rank of a multi-rank torch.distributed job."""
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+
+def SparseVFC_sharded(X, Y, Grid, M=100, a=5, beta=None, ecr=1e-5, gamma=0.9, lambda_=3, minP=1e-5, MaxIter=500,
+                      theta=0.75, velocity_based_sampling=True, seed=0, lstsq_method="drouin", comm=None, gather=True,
+                      dst=0):
+    """SparseVFC (scVectorField.py:313-542) over cells sharded across the ranks of a torchrun job: `X`, `Y` are THIS
+    rank's contiguous row block of the cell matrix (rank order = row order).  One joint fit: sharded_prelude fixes
+    the control points of the whole data set, the EM loop allreduces the Gram/RHS block per iteration.
+
+    gather=True: rank `dst` returns the VecFldDict of the whole data set -- the same keys, shapes and index
+    conventions as a single-GPU SparseVFC of the concatenated rows (`X`, `Y`, `V`, `P`, `valid_ind`, `VFCIndex`
+    gathered in row order).  Every other rank (and every rank with gather=False) returns the dict of its own rows:
+    local `X`, `Y`, `V`, `P`, `valid_ind`, `VFCIndex` (local row numbers; `row_offset` gives the global number of
+    its first row) next to the replicated `X_ctrl`, `ctrl_idx`, `beta`, `C`, `sigma2`, `iteration`, `tecr_traj`,
+    `E_traj`, `grid`, `grid_V` -- enough for `vector_field_function` / Jacobian / divergence ... on its own cells."""
+    from .device import host
+    from .sparsevfc import solver_code
+    from . import kernels
+
+    comm = comm or default_comm()
+    rank, world = dist.get_rank(), dist.get_world_size()
+    solver = solver_code(lstsq_method)
+    X_ori, Y_ori = np.array(X, copy=True), np.array(Y, copy=True)
+    Xd, Yd = dev(X), dev(Y)
+    st, ctrl_t, idx, beta, valid = fit_sharded(Xd, Yd, M, comm, seed=seed, beta=beta,
+                                               velocity_based_sampling=velocity_based_sampling, a=a, gamma=gamma,
+                                               lambda_=lambda_, minP=minP, ecr=ecr, theta=theta, MaxIter=MaxIter,
+                                               solver=solver)
+    if st.n_iter == 0:
+        raise Exception(
+            "please check your input parameters, "
+            f"tecr: 1, ecr {ecr} and sigma2 {st.sigma2},"
+            f"tecr must larger than ecr and sigma2 must larger than 1e-8"
+        )
+    i = st.n_iter
+    n_rows = torch.tensor([Xd.shape[0]], dtype=torch.int64, device=Xd.device)
+    all_rows = [torch.zeros_like(n_rows) for _ in range(world)]
+    dist.all_gather(all_rows, n_rows)
+    all_rows = [int(c.item()) for c in all_rows]
+    offset = int(sum(all_rows[:rank]))
+    ctrl = ctrl_t.cpu().numpy()
+    shared = {
+        "X_ctrl": ctrl, "ctrl_idx": idx, "beta": beta, "C": host(st.C), "sigma2": st.sigma2, "grid": Grid,
+        "grid_V": None, "iteration": i - 1, "tecr_traj": host(st.tecr_traj)[:i], "E_traj": host(st.E_traj)[:i],
+    }
+    if Grid is not None:
+        shared["grid_V"] = host(kernels.eval_field(Grid, ctrl_t, beta, st.C))
+    if gather:
+        Xg, _ = gather_rows(Xd, dst)
+        Yg, _ = gather_rows(Yd, dst)
+        Vg, _ = gather_rows(st.V, dst)
+        Pg, _ = gather_rows(st.P.reshape(-1, 1), dst)
+        vg, _ = gather_rows(valid + offset, dst)
+        if rank == dst:
+            P = host(Pg)
+            return dict(shared, X=host(Xg), valid_ind=host(vg), Y=host(Yg), V=host(Vg), P=P,
+                        VFCIndex=np.where(P > theta)[0])
+    P = host(st.P).reshape(-1, 1)
+    return dict(shared, X=X_ori, valid_ind=host(valid), Y=Y_ori, V=host(st.V), P=P, VFCIndex=np.where(P > theta)[0],
+                row_offset=offset)

@@ -341,6 +341,20 @@ def solve(G, Kc, M, D, lam_sigma2):
     return Cm, int(info.item())
 
 
+def solve_normal(G, Kc, M, D, lam_sigma2):
+    """The reference's solver form, tools/utils.py:2975-2976: C = solve(lhs^T lhs, lhs^T rhs) by LU with partial
+    pivoting (lhs = G[:M,:M] + lam_sigma2 Kc, rhs = G[M:M+D,:M]^T).  Returns C (M x D), info."""
+    G, Kc = dev(G), dev(Kc)
+    nbytes = C.c_size_t(0)
+    _lib.check(lib().dvf_solve_normal_workspace_bytes(int(M), int(D), C.byref(nbytes)))
+    ws = torch.empty((nbytes.value + 7) // 8, dtype=torch.float64, device="cuda")
+    Cm = empty((M, D))
+    info = torch.zeros((1,), dtype=torch.int32, device="cuda")
+    _lib.check(lib().dvf_solve_normal(ptr(G), G.shape[1], ptr(Kc), int(M), int(D), float(lam_sigma2), ptr(ws),
+                                      nbytes.value, ptr(Cm), ptr(info), stream_ptr()))
+    return Cm, int(info.item())
+
+
 def update_v(UY, Cm, P, minP, D, M):
     """scVectorField.py:484-486.  Returns V, r2, sum max(P,minP) r2."""
     UY, Cm, P = dev(UY), dev(Cm), dev(P).reshape(-1)

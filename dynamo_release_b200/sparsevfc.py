@@ -35,8 +35,23 @@ class FitState:
         self.workspace = None
 
 
+def solver_code(lstsq_method):
+    """`lstsq_method` of SparseVFC (scVectorField.py:185-194) -> DVF_SOLVER_*.
+
+    "drouin" (the reference's default; also what the reference falls back to for an unknown name, :191-193): the
+    reference's own form, normal equations solve(lhs^T lhs, lhs^T rhs) by LU with partial pivoting, on the device.
+    "cholesky": an addition of this backend -- factor the symmetric positive definite lhs itself (error cond eps
+    instead of cond^2 eps; what round 1 always did).  "scipy" (scipy.linalg.lstsq, an SVD) is not built."""
+    if lstsq_method == "cholesky":
+        return _lib.SOLVER_CHOLESKY
+    if lstsq_method == "scipy":
+        raise NotImplementedError("lstsq_method='scipy' (scipy.linalg.lstsq / SVD) is not served by the B200 backend; "
+                                  "use 'drouin' (the reference's default) or 'cholesky'")
+    return _lib.SOLVER_NORMAL_LU
+
+
 def fit_em(X, Y, Xc, beta, a=5, gamma=0.9, lambda_=3, minP=1e-5, ecr=1e-5, theta=0.75, MaxIter=500,
-           comm=None, N_total=None, check_every=0, workspace=None) -> FitState:
+           comm=None, N_total=None, check_every=0, workspace=None, solver=_lib.SOLVER_NORMAL_LU) -> FitState:
     """EM loop of scVectorField.py:417-497 on device tensors X, Y (N x D, valid rows only), Xc (M x D)."""
     X, Y, Xc = dev(X), dev(Y), dev(Xc)
     N, D = X.shape
@@ -57,7 +72,7 @@ def fit_em(X, Y, Xc, beta, a=5, gamma=0.9, lambda_=3, minP=1e-5, ecr=1e-5, theta
     st.E_traj = torch.full((n_traj,), float("nan"), dtype=torch.float64, device="cuda")
     st.tecr_traj = torch.full((n_traj,), float("nan"), dtype=torch.float64, device="cuda")
     prm = _lib.EmParams(float(a), float(gamma), float(lambda_), float(minP), float(ecr), float(theta),
-                        int(MaxIter), int(check_every))
+                        int(MaxIter), int(check_every), int(solver), 0)
     res = _lib.EmResult()
     _lib.check(L.dvf_fit_em(ptr(X), ptr(Y), N, int(N if N_total is None else N_total), D, ptr(Xc), M, float(beta),
                             C.byref(prm), ptr(st.C), ptr(st.P), ptr(st.V), ptr(st.E_traj), ptr(st.tecr_traj),
@@ -73,10 +88,24 @@ def SparseVFC(X, Y, Grid, M=100, a=5, beta=None, ecr=1e-5, gamma=0.9, lambda_=3,
     """Drop-in for dynamo's SparseVFC (scVectorField.py:313-333).  Returns the VecFldDict with numpy values.
 
     Differences, all documented in DESIGN.md: the div/curl-free kernel branch raises NotImplementedError;
-    `lstsq_method` is accepted and ignored (the M x M system is solved by a Cholesky factorisation of lhs
-    on the device in every case)."""
+    `lstsq_method`: "drouin" (default) is the reference's normal-equations form on the device, "cholesky" is this
+    backend's stable alternative, "scipy" raises NotImplementedError (solver_code).  `sharded=True` (or the
+    environment variable DVF_SHARDED=1) inside a torchrun job: X, Y are this rank's row block and the fit is ONE
+    joint fit over all ranks (dist.SparseVFC_sharded)."""
     if div_cur_free_kernels:
         raise NotImplementedError("div_cur_free_kernels=True is outside the B200 hot path (Gaussian kernel only)")
+    solver = solver_code(lstsq_method)
+    sharded = _ignored.pop("sharded", None)
+    if sharded is None:
+        import os
+        sharded = os.environ.get("DVF_SHARDED", "0") not in ("", "0")
+    if sharded:
+        from . import dist as _dist
+        if _dist.active():
+            return _dist.SparseVFC_sharded(X, Y, Grid, M=M, a=a, beta=beta, ecr=ecr, gamma=gamma, lambda_=lambda_,
+                                           minP=minP, MaxIter=MaxIter, theta=theta,
+                                           velocity_based_sampling=velocity_based_sampling, seed=seed,
+                                           lstsq_method=lstsq_method, gather=_ignored.pop("gather", True))
     # the reference copies its inputs (:396); the two host copies run on helper threads (NumPy releases the GIL)
     # while this thread uploads the data and drives the GPU
     copies = _copy_pool().map(lambda a: np.array(a, copy=True), (X, Y))
@@ -87,7 +116,7 @@ def SparseVFC(X, Y, Grid, M=100, a=5, beta=None, ecr=1e-5, gamma=0.9, lambda_=3,
     if N == 0:
         raise Exception("no cell with a finite velocity vector")
     st = fit_em(Xv, Yv, ctrl, beta, a=a, gamma=gamma, lambda_=lambda_, minP=minP, ecr=ecr, theta=theta,
-                MaxIter=MaxIter)
+                MaxIter=MaxIter, solver=solver)
     if st.n_iter == 0:
         # reference :498-503 -- the loop never ran
         raise Exception(

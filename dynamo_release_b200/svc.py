@@ -128,7 +128,7 @@ class SvcVectorField:
         verbose = kwargs.pop("verbose", 0)
         lstsq_method = kwargs.pop("lstsq_method", "drouin")
         known = ("M", "a", "beta", "ecr", "gamma", "lambda_", "minP", "MaxIter", "theta", "div_cur_free_kernels",
-                 "velocity_based_sampling", "sigma", "eta", "seed")
+                 "velocity_based_sampling", "sigma", "eta", "seed", "sharded", "gather")
         params = {k: v for k, v in self.parameters.items() if k in known}
         VecFld = SparseVFC(self.data["X"], self.data["V"], self.data["Grid"], **params, verbose=verbose,
                            lstsq_method=lstsq_method)
@@ -137,8 +137,9 @@ class SvcVectorField:
         self.func = _vf.RkhsField(VecFld)
         # :1043 evaluates f on ALL rows and overwrites the EM's V.  When every row is valid that is the same
         # product U C the loop just left in V, so it is only recomputed when rows were dropped.
-        if len(VecFld["valid_ind"]) != len(self.data["X"]):
-            self.vf_dict["V"] = self.func(self.data["X"])
+        # (VecFld["X"] is the copy of data["X"]; in a sharded fit with gather it holds the rows of ALL ranks on rank 0)
+        if len(VecFld["valid_ind"]) != len(VecFld["X"]):
+            self.vf_dict["V"] = self.func(VecFld["X"])
         self.vf_dict["normalize"] = self.normalize
         return self.vf_dict
 

@@ -163,7 +163,16 @@ typedef struct dvf_em_params {
     double theta;    /* inlier threshold on P, default 0.75                        (:322) */
     int max_iter;    /* MaxIter, default 500 (30 through VectorField)              (:321) */
     int check_every; /* iterations launched between host reads of the stop flag; 0 = default (8) */
+    int solver;      /* DVF_SOLVER_*: how the M x M system of the M-step is solved (lstsq_method, :332)  */
+    int reserved;
 } dvf_em_params;
+
+/* lstsq_method="drouin" (the reference's default, tools/utils.py:2948-2981): normal equations
+ * solve(lhs^T lhs, lhs^T rhs) by LU with partial pivoting -- squares cond(lhs) exactly as the reference does. */
+#define DVF_SOLVER_NORMAL_LU 1
+/* Cholesky factorisation of the symmetric positive definite lhs itself: same solution in exact arithmetic,
+ * error cond(lhs) eps instead of cond(lhs)^2 eps (lstsq_method="cholesky", an addition of this backend). */
+#define DVF_SOLVER_CHOLESKY 0
 
 /* scalars the EM loop leaves on the host when it returns */
 typedef struct dvf_em_result {
@@ -210,6 +219,12 @@ int dvf_gram(const double* UY, const double* P, double minP, int64_t N, int D, i
  * L: (M + D) x M scratch.  info (device int): 0 ok, k>0 = non-positive pivot at column k-1. */
 int dvf_solve(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
               double* L, double* C, int* info, void* stream);
+/* The reference's solver form (DVF_SOLVER_NORMAL_LU) as a step: C = solve(lhs^T lhs, lhs^T rhs), LU with partial
+ * pivoting (tools/utils.py:2975-2976 -> LAPACK gesv).  ws: dvf_solve_normal_workspace_bytes(); info: 0 ok, k>0 =
+ * exactly zero pivot at column k-1 (numpy raises LinAlgError("Singular matrix") there). */
+int dvf_solve_normal_workspace_bytes(int M, int D, size_t* out);
+int dvf_solve_normal(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
+                     void* ws, size_t ws_bytes, double* C, int* info, void* stream);
 /* V = U C, r2 = |Y - V|^2 per cell, stats[0] = sum_n max(P,minP)_n r2_n.   scVectorField.py:484-486 */
 int dvf_update_v(const double* UY, const double* C, const double* P, double minP, int64_t N, int D,
                  int M, double* V, double* r2, double* stats, void* stream);

@@ -38,6 +38,34 @@ def main():
             print("world=%d n=%d d=%d M=%d: iters %d vs %d, relC %.3g relV %.3g sigma2 %.6g vs %.6g ctrl-equal %s"
                   % (world, n, d, m, st.n_iter, s1.n_iter, relC, relV, st.sigma2, s1.sigma2, same), flush=True)
             ok = ok and same and st.n_iter == s1.n_iter and relC < tol and relV < tol
+    # the product API: SvcVectorField(..., sharded=True) inside the torchrun job returns the VecFldDict of the WHOLE data
+    # set on rank 0 (scVectorField.py:509-532 layout), equal to the single-GPU dict of the concatenated rows
+    import dynamo_release_b200 as dvf
+    n, d, m = 50001, 30, 100
+    X, V = hematopoiesis_like(n, d, seed=11, velocity_scale=1.0)
+    V[[7, n - 3]] = np.nan
+    lo, hi = shard_bounds(n, world, rank)
+    for method in ("drouin", "cholesky"):
+        vfc = dvf.SvcVectorField(X[lo:hi], V[lo:hi], None, normalize=False, M=m, MaxIter=12, sharded=True)
+        got = vfc.train(lstsq_method=method)
+        loc = vfc.compute_divergence()          # evaluation of the rank's own rows needs no exchange
+        assert loc.shape == (hi - lo,)
+        if rank == 0:
+            one = dvf.SvcVectorField(X, V, None, normalize=False, M=m, MaxIter=12).train(lstsq_method=method)
+            same_keys = set(got.keys()) == set(one.keys())
+            exact = all(np.array_equal(got[k], one[k]) for k in ("X", "valid_ind", "X_ctrl", "ctrl_idx", "VFCIndex")) \
+                and np.array_equal(got["Y"], one["Y"], equal_nan=True) and got["iteration"] == one["iteration"] \
+                and got["beta"] == one["beta"]
+            rels = {k: float(np.max(np.abs(got[k] - one[k])) / np.max(np.abs(one[k]))) for k in
+                    ("V", "C", "P", "E_traj", "tecr_traj")}
+            rels["sigma2"] = abs(got["sigma2"] - one["sigma2"]) / one["sigma2"]
+            good = same_keys and exact and all(v < 1e-10 for k, v in rels.items() if k != "tecr_traj")
+            print("world=%d API dict (%s): keys equal %s, index/identity fields exact %s, rel %s -> %s"
+                  % (world, method, same_keys, exact, {k: "%.2g" % v for k, v in rels.items()}, "ok" if good else "FAIL"),
+                  flush=True)
+            ok = ok and good
+    from dynamo_release_b200.dist import close_default_comm
+    close_default_comm()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, 0)
     comm.close()

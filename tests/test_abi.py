@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, n), "libdvf_b200.so does not export %s" % n
     # and the ctypes table covers the header one to one
     assert sorted(_lib.SIGNATURES) == names
-    assert lib.dvf_abi_version() == 1
+    assert lib.dvf_abi_version() == 2
 
 
 def test_argument_errors_are_reported_without_a_gpu():

@@ -35,7 +35,10 @@ def test_calculus_fixed_C_matches_reference(pkg, name):
     vf = g.vf()
     xs = g.X[g["calc_cells"]]
     nj = g["calc_J"].shape[2]
-    assert rel(pkg.vector_field_function(xs, vf), g["calc_f"]) < 1e-12
+    # f = K C cancels when the coefficients are large (the ill-conditioned fits: max|C| 1.4e3 against max|f| 1.7 at the
+    # C5-shaped case): the rounding of either side is eps * sum|k C|, so the gate scales with max|C| / max|f|
+    amp = max(1.0, float(np.abs(vf["C"]).max() / np.abs(g["calc_f"]).max()))
+    assert rel(pkg.vector_field_function(xs, vf), g["calc_f"]) < 1e-12 * amp
     assert rel(pkg.Jacobian_rkhs_gaussian(xs[:nj], vf), g["calc_J"]) < 1e-11
     J1 = pkg.Jacobian_rkhs_gaussian(xs[0], vf)
     assert J1.shape == g["calc_J_single"].shape and rel(J1, g["calc_J_single"]) < 1e-11
@@ -158,11 +161,25 @@ def test_em_steps_teacher_forced(pkg, name):
         C_exact = _exact_solve(lhs, g["trace_rhs_%d" % it])
         err_gpu, err_ref = rel(C_gpu, C_exact), rel(g["trace_C_%d" % it], C_exact)
         assert err_gpu <= max(1e-9, 2 * err_ref), (err_gpu, err_ref)
+        # solver, the reference's own form (lstsq_method="drouin": normal equations + LU with partial pivoting, the
+        # default): it and the reference's C are two roundings of the same cond^2-amplified computation, so they agree
+        # to ~cond^2 eps (a real gate where cond^2 eps << 1) and ours is in the reference's error class w.r.t. the
+        # exact solution
+        C_nrm, info = k.solve_normal(G, Kc, M, D, p["lambda_"] * sigma2)
+        assert info == 0
+        C_nrm = _np(C_nrm)
+        cond = float(np.linalg.cond(lhs))
+        d_ref, err_nrm = rel(C_nrm, g["trace_C_%d" % it]), rel(C_nrm, C_exact)
+        print("\n[%s it %d] cond(lhs) %.2g  |C_drouin - C_ref| %.2g (cond^2 eps %.2g)  vs exact: drouin %.2g, ref %.2g, "
+              "cholesky %.2g" % (name, it, cond, d_ref, cond**2 * 2.2e-16, err_nrm, err_ref, err_gpu))
+        assert d_ref <= max(1e-12, 20 * cond**2 * 2.2e-16) or d_ref <= 4 * err_ref
+        assert err_nrm <= max(1e-9, 20 * err_ref, 20 * cond**2 * 2.2e-16)
         # continue from the REFERENCE's C (teacher forcing): V = U C, r2, sum P r2
         C_ref = g["trace_C_%d" % it]
         V, r2_t, st = k.update_v(UY, C_ref, P, p["minP"], D, M)
         V_ref = U_ref.dot(C_ref)
-        assert rel(_np(V), V_ref) < 1e-12
+        amp = max(1.0, float(np.abs(C_ref).max() / np.abs(V_ref).max()))   # cancellation in U C (see the calculus test)
+        assert rel(_np(V), V_ref) < 1e-12 * amp
         r2 = np.sum((Y - V_ref) ** 2, 1)
         assert rel(_np(r2_t), r2) < 1e-10
         Pc = np.maximum(_np(P), p["minP"])
@@ -181,8 +198,9 @@ def _e2e_report(g, vf, name):
     return ours, floor
 
 
+@pytest.mark.parametrize("lstsq_method", ["drouin", "cholesky"])
 @pytest.mark.parametrize("name", CASES)
-def test_fit_end_to_end(pkg, name):
+def test_fit_end_to_end(pkg, name, lstsq_method):
     """End-to-end fit against the executed reference.  Where the reference reproduces itself (permutation floor of V
     below 1e-9) everything is gated at 1e-8 and iteration counts / index arrays are exact.  Elsewhere ("chaotic": the
     normal-equations solve amplifies 1e-16 differences in lhs by cond(lhs)^2) nothing is waived:
@@ -191,7 +209,7 @@ def test_fit_end_to_end(pkg, name):
     K = 20.0
     g = Golden(name)
     fc, fv = g.floor()
-    vf = pkg.SvcVectorField(g.X.copy(), g.V.copy(), None, normalize=False, **g.params).train()
+    vf = pkg.SvcVectorField(g.X.copy(), g.V.copy(), None, normalize=False, **g.params).train(lstsq_method=lstsq_method)
     s = g.stride
     assert np.array_equal(vf["ctrl_idx"], g["final_ctrl_idx"])
     assert np.array_equal(vf["X_ctrl"], g["final_X_ctrl"])
@@ -205,9 +223,9 @@ def test_fit_end_to_end(pkg, name):
     chaotic = (fv > 1e-9) or not same_ctrl and name.startswith("toggle")
     dv, dc = rel(vf["V"][::s], g["final_Vfit"]), rel(vf["C"], g["final_C"])
     pre, pre_floor = prefix_len(vf["E_traj"], g["final_E_traj"]), g.floor_prefix()
-    print("\n[%s] iters %d (ref %d, ref refit %d)  relV %.3g (floor %.3g)  relC %.3g (floor %.3g)  E-prefix@1e-8 %d "
+    print("\n[%s, %s] iters %d (ref %d, ref refit %d)  relV %.3g (floor %.3g)  relC %.3g (floor %.3g)  E-prefix@1e-8 %d "
           "(ref refit %d)\n    relE ours : %s\n    relE floor: %s"
-          % (name, vf["iteration"] + 1, int(g["final_iteration"]) + 1, int(g["floor_iteration"]) + 1, dv, fv, dc, fc,
+          % (name, lstsq_method, vf["iteration"] + 1, int(g["final_iteration"]) + 1, int(g["floor_iteration"]) + 1, dv, fv, dc, fc,
              pre, pre_floor, np.array2string(ours, precision=1), np.array2string(floor, precision=1)))
     if not chaotic:
         tolC, tolV = max(1e-8, K * fc), max(1e-8, K * fv)
