@@ -230,8 +230,10 @@ __global__ void __launch_bounds__(IVP_THREADS) k_ivp_rk45(const double* __restri
         t = t_new;
         if (dir * (t - t_bound) >= 0.0) done = true;
         const bool rest_new = ivp_at_rest(s.K[6], D, rest_tol);   // K[6] = f(y_new), visible since ivp_field returned
-        if (rest_new) {
-            // terminal event: the two-valued event function makes the bracketing root finder return an end point
+        if (rest_new || rest_old) {
+            // terminal event: the two-valued event function (0 at rest, -1 otherwise) makes the bracketing root finder
+            // return an end point.  scipy's find_active_events fires on -1 -> 0 (root = t), 0 -> 0 and 0 -> -1 (a start at
+            // rest: root = t_old, so the result is t = [t0, t0]); the last two can only happen on the first step.
             const double root = rest_old ? t_old : t;
             const double x = (root - t_old) / h;
             if (tid < D) {
@@ -575,7 +577,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
                 accept[tr] = true;
                 t[tr] = t_new[tr];
                 if (dir * (t[tr] - t_bound) >= 0.0) stop[tr] = true;
-                if (rest_new[tr]) {
+                if (rest_new[tr] || rest_old[tr]) {      // incl. a start at rest that leaves it: root = t_old
                     const double root = rest_old[tr] ? t_old[tr] : t[tr];
                     xroot[tr] = (root - t_old[tr]) / h[tr];
                     t[tr] = root;
@@ -588,7 +590,7 @@ __global__ void __launch_bounds__(IVP_THREADS, MINB) k_ivp_rk45_t(const double* 
             }
         }
         const bool my_accept = ivp_pick(accept, my);
-        const bool my_rest = my_accept && ivp_pick(rest_new, my);
+        const bool my_rest = my_accept && (ivp_pick(rest_new, my) || ivp_pick(rest_old, my));
         const int my_nst = ivp_pick(nst, my);
         if (my_accept) {
             const double x = ivp_pick(xroot, my);

@@ -149,9 +149,12 @@ def _field_of(f, probes=None):
     SvcVectorField.func / vecfld_from_adata return) are taken as they are.  A plain function -- dynamo builds
     `lambda x: scale * vector_field_function(x=x, vf_dict=VecFld, dim=dims)` in prediction/fate.py:133-135 and
     scVectorField.py:764-766 -- is called on a few of the initial states with a trace open on vector_field_function
-    (vf._TRACE): if every call evaluated one and the same RKHS field over all its dimensions and the output is one
-    constant times that value, the callable IS scale x field and runs on the device.  Anything else is refused: there
-    is no CPU path for arbitrary Python callables."""
+    (vf._TRACE): if every call evaluated one and the same RKHS field over all its dimensions AT THE POINT IT WAS GIVEN
+    (a wrapper that rescales or shifts its argument first, `lambda x: vff((x - xm) / xscale, vf)`, is not the field)
+    and the output is one constant times that value, the callable IS scale x field and runs on the device.  At least
+    three distinct points are probed (perturbed copies of the states are added when fewer are given), so a factor that
+    depends on the state (`lambda x: vff(x, vf) * x[0]`) is seen to vary.  Anything else is refused: there is no CPU
+    path for arbitrary Python callables."""
     from . import vf as _vf
 
     vf_dict = getattr(f, "vf_dict", None)
@@ -164,7 +167,13 @@ def _field_of(f, probes=None):
     if probes is None or len(probes) == 0 or not callable(f):
         raise refuse
     pairs, fields = [], []
-    for x in np.atleast_2d(probes)[:3]:
+    pts = [np.array(x, dtype=np.float64) for x in np.atleast_2d(probes)[:3]]
+    k = 0
+    while len(pts) < 3:                     # perturbed copies: distinct points even for a single initial state
+        base = pts[k % len(pts)]
+        k += 1
+        pts.append(base * (1.0 + 0.03125 * k) + 0.0078125 * k * (1.0 + np.abs(base).max()))
+    for x in pts:
         _vf._TRACE.rec = rec = []
         try:
             out = np.asarray(f(np.array(x, dtype=np.float64)))
@@ -172,7 +181,9 @@ def _field_of(f, probes=None):
             _vf._TRACE.rec = None
         if len(rec) != 1:
             raise refuse
-        d, dim, ctrl_ind, res = rec[0]
+        x_seen, d, dim, ctrl_ind, res = rec[0]
+        if x_seen.shape != x.shape or not np.array_equal(x_seen, x):
+            raise refuse                        # the callable evaluates the field somewhere else than at its argument
         res = np.asarray(res)
         n_dim = np.shape(d["X_ctrl"])[1]
         full = dim is None or (np.isscalar(dim) and dim == n_dim) or \

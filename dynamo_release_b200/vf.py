@@ -59,10 +59,10 @@ def con_K(x, y, beta=0.1, method="cdist", return_d=False, timeit=False, device_o
 _TRACE = threading.local()
 
 
-def _record_trace(vf_dict, dim, X_ctrl_ind, result):
+def _record_trace(x, vf_dict, dim, X_ctrl_ind, result):
     rec = getattr(_TRACE, "rec", None)
     if rec is not None:
-        rec.append((vf_dict, dim, X_ctrl_ind, result))
+        rec.append((np.array(x, dtype=np.float64, copy=True), vf_dict, dim, X_ctrl_ind, result))
 
 
 def vector_field_function(x, vf_dict, dim=None, kernel="full", X_ctrl_ind=None, timeit=False, device_out=False,
@@ -84,7 +84,8 @@ def vector_field_function(x, vf_dict, dim=None, kernel="full", X_ctrl_ind=None, 
     if dim is not None:
         v = v[..., :dim] if np.isscalar(dim) else v[..., dim]
     res = _out(v, device_out)
-    _record_trace(vf_dict, dim, X_ctrl_ind, res)
+    if getattr(_TRACE, "rec", None) is not None:
+        _record_trace(host(x) if isinstance(x, torch.Tensor) else x, vf_dict, dim, X_ctrl_ind, res)
     return res
 
 

@@ -129,7 +129,9 @@ def rk45_solve(fun, t0, t_bound, y0, max_step=np.inf, rtol=1e-3, atol=1e-6):
         if direction * (t - t_bound) >= 0:
             status = FINISHED
         rest_new = _at_rest(f)
-        if rest_new:
+        if rest_new or rest_old:
+            # find_active_events: the event function (0 at rest, -1 otherwise) fires on -1 -> 0 (brentq returns t),
+            # 0 -> 0 and 0 -> -1 (a start at rest; brentq returns t_old, so t = [t0, t0])
             root = t_old if rest_old else t
             x = (root - t_old) / h
             p = np.cumprod(np.tile(x, 4))

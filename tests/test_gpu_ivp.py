@@ -182,6 +182,19 @@ def test_lambda_wrapped_field_runs_on_the_device(it):
         assert np.array_equal(u, v)
     with pytest.raises(NotImplementedError):
         it.integrate_vf_ivp(y0, t, "forward", lambda x: -x)
+    # wrappers that are NOT scale x field are refused, also with a single initial state (round-1 advisor finding):
+    # the field evaluated somewhere else than at the argument, and a state-dependent factor
+    for bad in (lambda x: dvf.vector_field_function(x * 2 + 1, vf),
+                lambda x: dvf.vector_field_function((x - 0.5) / 3.0, vf),
+                lambda x: dvf.vector_field_function(x, vf) * x[..., :1],
+                lambda x: dvf.vector_field_function(x, vf) * np.atleast_2d(x)[0, 0]):
+        for states in (y0, y0[:1]):
+            with pytest.raises(NotImplementedError):
+                it.integrate_vf_ivp(states, t, "forward", bad)
+    # ... while the genuine form is still recognised from one state
+    one = it.integrate_vf_ivp(y0[:1], t, "forward", lambda x: scale * dvf.vector_field_function(x, vf), interpolation_num=20)
+    two = it.integrate_vf_ivp(y0[:1], t, "forward", it.ScaledRkhsField(vf, scale), interpolation_num=20)
+    assert np.array_equal(one[1][0], two[1][0])
 
 
 def test_svc_integrate_method(it):

@@ -115,6 +115,18 @@ def test_start_at_rest_like_scipy():
     assert np.array_equal(r.sol(np.array([0.0, 5e-7])), io.dense_eval(g, np.array([0.0, 5e-7])))
 
 
+def test_start_at_rest_and_leave_it_like_scipy():
+    """Round-1 advisor finding: a start just under the at-rest threshold on a growing field.  The event function goes
+    0 -> -1 over the first step; scipy's find_active_events fires on that too and brentq returns t_old: t = [t0, t0],
+    status 1."""
+    f = lambda x: 9e-6 + 1e5 * x  # noqa: E731
+    y0 = np.array([0.0])
+    r = _scipy_call(f, 0.0, 1.0, y0, 0.1)
+    g = io.rk45_solve(f, 0.0, 1.0, y0, max_step=0.1)
+    assert r.status == g["status"] == 1
+    assert np.array_equal(r.t, g["t"]) and np.array_equal(r.t, [0.0, 0.0]) and np.array_equal(r.y, g["y"])
+
+
 def test_large_cell_sets_are_sliced_without_changing_results(monkeypatch):
     """More cells than the HBM budget for resident dense solutions: solve -> resample -> evaluate runs per slice."""
     from dynamo_release_b200 import integrate as it
@@ -164,7 +176,7 @@ def _traced_vff(x, vf_dict, dim=None, X_ctrl_ind=None):
     r = vo.field_eval(x, vf_dict)
     if dim is not None:
         r = r[..., :dim] if np.isscalar(dim) else r[..., dim]
-    vfm._record_trace(vf_dict, dim, X_ctrl_ind, r)
+    vfm._record_trace(x, vf_dict, dim, X_ctrl_ind, r)
     return r
 
 
@@ -187,10 +199,18 @@ def test_lambda_wrapped_fields_are_recognised(monkeypatch):
                lambda x: _traced_vff(x, vf, dim=2),                                # a subset of the dimensions
                lambda x: _traced_vff(x, vf, X_ctrl_ind=[0, 1]),
                lambda x: _traced_vff(x, vf) + _traced_vff(x, other),              # two evaluations
-               lambda x: _traced_vff(x, vf if x[0] > probes[1, 0] else other)]     # different fields per call
+               lambda x: _traced_vff(x, vf if x[0] > probes[1, 0] else other),     # different fields per call
+               lambda x: _traced_vff(x * 2 + 1, vf),                               # the field somewhere else than at x
+               lambda x: _traced_vff((x - 0.25) / 1.5, vf)]                        # (a normalising wrapper)
     for g in refused:
         with pytest.raises(NotImplementedError):
             it._field_of(g, probes)
+    # a single initial state: perturbed copies are probed too, so a state-dependent factor is still seen to vary
+    for g in (lambda x: _traced_vff(x, vf) * x[0], lambda x: _traced_vff(x * 2 + 1, vf)):
+        with pytest.raises(NotImplementedError):
+            it._field_of(g, probes[:1])
+    d, s = it._field_of(lambda x: 0.7 * _traced_vff(x, vf), probes[:1])
+    assert d is vf and s == 0.7
     # and end to end (oracle standing in for the device solver): same lists as with the field object
     monkeypatch.setattr(it, "solve_ivp_batch", ivp_util.oracle_batch(it.DenseSolution, it.IvpResult))
     t = np.linspace(0, 2.0, 5)
