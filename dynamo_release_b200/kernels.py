@@ -72,6 +72,7 @@ def jacobian_to_host(x, Xc, beta, Cm):
     ch = min(JAC_STREAM_CHUNK, n)
     bufs = [torch.empty((D * D * ch,), dtype=torch.float64, device="cuda") for _ in range(2 if n > ch else 1)]
     main, side = torch.cuda.current_stream(), _side_stream()
+    side.wait_stream(main)
     copied = [None, None]
     L = lib()
     for k, c0 in enumerate(range(0, n, ch)):
@@ -144,6 +145,10 @@ def div_acc_curv_host(X, Xc, beta, Cm, formula=2, want=("acc", "acc_norm")):
     xin = [torch.empty((ch, D), dtype=torch.float64, device="cuda") for _ in range(nbuf)]
     dout = [{k: torch.empty((ch,) + shapes[k][1:], dtype=torch.float64, device="cuda") for k in want} for _ in range(nbuf)]
     main, s_in, s_out = torch.cuda.current_stream(), _in_stream(), _side_stream()
+    # the slab buffers above come from the caching allocator in `main`'s order: work still queued on `main` may be using
+    # the recycled blocks, so the side streams start behind it
+    s_in.wait_stream(main)
+    s_out.wait_stream(main)
     Xt = torch.from_numpy(Xh)
     computed, drained = [None] * nbuf, [None] * nbuf
     L = lib()

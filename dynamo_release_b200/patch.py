@@ -39,17 +39,40 @@ _MODULES = ("dynamo.vectorfield.utils", "dynamo.vectorfield.scVectorField", "dyn
             "dynamo.vectorfield.VectorField", "dynamo.vectorfield.rank_vf", "dynamo.vectorfield", "dynamo.vf", "dynamo.prediction.utils",
             "dynamo.prediction.fate")
 _saved = {}
+_combined = {}
+
+
+def _svc_class():
+    """The class bound to the name SvcVectorField: this package's class with dynamo's own SvcVectorField as a second
+    base, so that the methods outside the hot path (find_fixed_points, get_fixed_points, assign_fixed_points,
+    construct_graph, plot_energy, evaluate: scVectorField.py:569-719, 1048-1164) keep working on the same
+    `data` / `vf_dict` / `func` attributes; every hot-path method resolves to the B200 one first."""
+    if "cls" in _combined:
+        return _combined["cls"]
+    try:
+        ref = importlib.import_module("dynamo.vectorfield.scVectorField").SvcVectorField
+    except Exception:
+        return svc.SvcVectorField
+    if isinstance(ref, type) and issubclass(ref, svc.SvcVectorField):   # already installed
+        return ref
+    _combined["cls"] = type("SvcVectorField", (svc.SvcVectorField, ref), {
+        "__doc__": svc.SvcVectorField.__doc__, "__module__": svc.SvcVectorField.__module__})
+    return _combined["cls"]
 
 
 def install(modules=_MODULES):
     """Returns the list of (module, name) pairs that were rebound."""
     done = []
+    names = dict(_NAMES)
+    if not _saved:
+        _combined.clear()
+    names["SvcVectorField"] = _svc_class()
     for modname in modules:
         try:
             mod = importlib.import_module(modname)
         except Exception:
             continue
-        for name, fn in _NAMES.items():
+        for name, fn in names.items():
             if hasattr(mod, name) and getattr(mod, name) is not fn:
                 _saved[(modname, name)] = getattr(mod, name)
                 setattr(mod, name, fn)
@@ -61,3 +84,4 @@ def uninstall():
     for (modname, name), orig in list(_saved.items()):
         setattr(importlib.import_module(modname), name, orig)
         del _saved[(modname, name)]
+    _combined.clear()

@@ -160,6 +160,12 @@ def velocity_weighted_choice(speed: np.ndarray, M: int, seed: int) -> np.ndarray
     rng = np.random.default_rng(seed)
     lib = _lib.load()
     total = numpy_sum(speed)
+    # Generator.choice's own input checks (numpy/random/_generator.pyx): p must be finite / non-negative / sum to 1, and
+    # replace=False needs at least `size` non-zero entries -- without them the loop below would never finish
+    if not np.isfinite(total) or not total > 0:
+        raise ValueError("probabilities contain NaN")          # p = speed / 0 (or a non-finite speed) is NaN
+    if int(np.count_nonzero(speed)) < M:
+        raise ValueError("Fewer non-zero entries in p than size")
     raw = _host_buffer("raw", n)
     found = np.zeros(M, dtype=np.int64)
     n_uniq = 0

@@ -55,7 +55,23 @@ def test_install_rebinds_every_holder_and_uninstall_restores(ref_modules):
     try:
         assert set(done) == set(before), set(before) ^ set(done)
         for (m, n) in before:
+            if n == "SvcVectorField":
+                continue
             assert getattr(ref_modules[m], n) is patch._NAMES[n]
+        # SvcVectorField: the B200 class first, dynamo's own class behind it for the methods outside the hot path
+        # (round-1 advisor finding: find_fixed_points & co. must survive install())
+        ref_cls = before[("dynamo.vectorfield.scVectorField", "SvcVectorField")]
+        new_cls = ref_modules["dynamo.vectorfield.scVectorField"].SvcVectorField
+        assert issubclass(new_cls, patch._NAMES["SvcVectorField"]) and issubclass(new_cls, ref_cls)
+        public = [n for n in dir(ref_cls) if not n.startswith("_") and callable(getattr(ref_cls, n))]
+        assert all(hasattr(new_cls, n) for n in public), [n for n in public if not hasattr(new_cls, n)]
+        for n in ("train", "get_Jacobian", "compute_divergence", "compute_acceleration", "compute_curvature",
+                  "from_adata", "integrate", "get_Hessian"):
+            assert getattr(new_cls, n) is getattr(patch._NAMES["SvcVectorField"], n), n
+        for n in ("find_fixed_points", "get_fixed_points", "construct_graph", "plot_energy"):
+            assert getattr(new_cls, n) is getattr(ref_cls, n), n
+        for mname in ("dynamo.vectorfield.VectorField", "dynamo.vectorfield.vector_calculus"):
+            assert getattr(ref_modules[mname], "SvcVectorField") is new_cls
         # the modules that imported the names with `from .utils import ...` hold their own references
         assert ("dynamo.vectorfield.vector_calculus", "Jacobian_rkhs_gaussian") in before or \
                ("dynamo.vectorfield.scVectorField", "Jacobian_rkhs_gaussian") in before

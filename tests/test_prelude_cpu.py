@@ -55,3 +55,23 @@ def test_velocity_weighted_choice_equals_numpy_generator_choice():
         for seed in (0, 1, 19491001):
             ref = np.random.default_rng(seed).choice(np.arange(n), size=M, p=speed / np.sum(speed), replace=False)
             assert np.array_equal(ref, prelude.velocity_weighted_choice(speed, M, seed)), (n, M, seed)
+
+
+def test_choice_input_validation_like_numpy():
+    """Round-1 advisor finding: Generator.choice raises for all-zero speeds / fewer non-zero entries than M; the restated
+    sampler must do the same instead of spinning (tools/sampling.py:242-245 -> numpy/random/_generator.pyx)."""
+    import pytest
+
+    from dynamo_release_b200 import prelude
+
+    speed = np.zeros(50)
+    with pytest.raises(ValueError):
+        np.random.default_rng(0).choice(50, size=5, p=speed / speed.sum() if speed.sum() else np.full(50, np.nan), replace=False)
+    with pytest.raises(ValueError, match="NaN"):
+        prelude.velocity_weighted_choice(speed, 5, 0)
+    speed[[3, 7, 11]] = 1.0
+    with pytest.raises(ValueError, match="Fewer non-zero"):
+        np.random.default_rng(0).choice(50, size=5, p=speed / speed.sum(), replace=False)
+    with pytest.raises(ValueError, match="Fewer non-zero"):
+        prelude.velocity_weighted_choice(speed, 5, 0)
+    assert sorted(prelude.velocity_weighted_choice(speed, 3, 0)) == [3, 7, 11]
