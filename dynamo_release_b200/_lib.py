@@ -56,6 +56,7 @@ SIGNATURES = {
     "dvf_jacobian_det": (_i, [_p, _i64, _i, _p, _p]),
     "dvf_cell_angles": (_i, [_p, _p, _i64, _i, _p, _p]),
     "dvf_row_norms": (_i, [_p, _i64, _i, _p, _p]),
+    "dvf_knn_dists": (_i, [_p, _i, _i, _i, _p, _p]),
     "dvf_hessian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
     "dvf_laplacian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
     "dvf_ivp_workspace_bytes": (_i, [_i, _i, C.POINTER(_sz)]),

@@ -344,3 +344,61 @@ extern "C" int dvf_laplacian(const double* x, int64_t n, int D, const double* Xc
     DVF_LAUNCH_CHECK();
     return DVF_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// bandwidth_selector (reference scVectorField.py:121-135): distances of every control point to its k nearest control
+// points (itself included), ascending.  One CTA per control point: the M squared distances -- accumulated dimension by
+// dimension with separate multiply and add, the order and rounding sklearn's trees use -- go to shared memory, a
+// bitonic network sorts them, the first k + 1 leave as square roots.  Replaces 3 D eager launches + a library top-k.
+// ---------------------------------------------------------------------------------------------------------
+namespace dvf {
+__global__ void __launch_bounds__(256) k_knn_dists(const double* __restrict__ Xc, int M, int D, int kk, int P2,
+                                                   double* __restrict__ out) {
+    extern __shared__ double d2[];
+    const int i = blockIdx.x;
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    for (int j = threadIdx.x; j < P2; j += blockDim.x) {
+        double s = inf;
+        if (j < M) {
+            s = 0.0;
+            for (int d = 0; d < D; ++d) {
+                const double t = __dsub_rn(Xc[(int64_t)i * D + d], Xc[(int64_t)j * D + d]);
+                s = __dadd_rn(s, __dmul_rn(t, t));
+            }
+        }
+        d2[j] = s;
+    }
+    __syncthreads();
+    for (int k = 2; k <= P2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < P2; t += blockDim.x) {
+                const int p = t ^ j;
+                if (p > t) {
+                    const double a = d2[t], b = d2[p];
+                    const bool up = (t & k) == 0;
+                    if ((a > b) == up) { d2[t] = b; d2[p] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    for (int j = threadIdx.x; j < kk; j += blockDim.x) out[(int64_t)i * kk + j] = sqrt(d2[j]);
+}
+}  // namespace dvf
+
+extern "C" int dvf_knn_dists(const double* Xc, int M, int D, int kk, double* out, void* stream) {
+    DVF_ARG(Xc && out && M >= 1 && D >= 1 && kk >= 1 && kk <= M, "bad argument");
+    int P2 = 1;
+    while (P2 < M) P2 <<= 1;
+    DVF_ARG(P2 <= 16384, "dvf_knn_dists serves up to 16384 control points (M = %d)", M);
+    const size_t smem = sizeof(double) * (size_t)P2;
+    if (smem > 48 * 1024) {
+        static bool attr = false;
+        if (!attr) {
+            DVF_CUDA(cudaFuncSetAttribute(dvf::k_knn_dists, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+            attr = true;
+        }
+    }
+    dvf::k_knn_dists<<<M, 256, smem, (cudaStream_t)stream>>>(Xc, M, D, kk, P2, out);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}

@@ -211,17 +211,26 @@ namespace dvf {
 //     i = dgemm(a.T, a.T, trans_b=True)          ->  N = lhs^T lhs
 //     x = np.linalg.solve(i, dgemm(a.T, b))      ->  LAPACK gesv: LU with partial pivoting of N, then the two
 //                                                    triangular solves applied to lhs^T rhs
-// One cooperative launch.  lhs is symmetric (lower triangle of the Gram mirrored + lambda sigma2 Kc), so
-// lhs^T [lhs | rhs] = lhs [lhs | rhs]: phase 1 is one tiled product into the augmented matrix N = [lhs^T lhs | lhs^T rhs]
-// (M x (M + D)); the right-hand sides ride along as extra columns, so the forward substitution of gesv happens during
-// the elimination.  LU: right-looking, panels of LU_NB columns; the panel is factored by CTA 0 with one matrix row per
-// thread held in registers (pivot = first entry of largest magnitude, LAPACK's idamax rule; row exchange through shared
-// memory), the other CTAs join for the row swaps + U12 = L11^-1 N12 and for the trailing update.  The back
-// substitution runs in CTA 0.  Squares cond(lhs) exactly as the reference does -- that is the point of this path.
+// Squares cond(lhs) exactly as the reference does -- that is the point of this path.
+// lhs is symmetric (lower triangle of the Gram mirrored + lambda sigma2 Kc), so lhs^T [lhs | rhs] = lhs [lhs | rhs]:
+//   k_lu_prep  builds AB = [lhs | rhs]                               (grid-wide)
+//   k_lu_ata   N = lhs AB, the augmented matrix [lhs^T lhs | lhs^T rhs] (M x (M + D)), tiles over the whole GPU
+//   k_lu_factor  ONE thread-block cluster (16 CTAs; 8 where 16 cannot be scheduled): right-looking LU with partial
+//              pivoting in panels of LU_NB columns, the right-hand sides riding along as extra columns (gesv's forward
+//              substitution happens during the elimination), then the back substitution.  The three phases of a panel
+//              are separated by cluster barriers (~0.2 us) instead of grid-wide ones; v1 of this kernel (cooperative
+//              grid of 40 CTAs x 1024 threads, 4 block barriers per column, rows physically exchanged) took 2.28 ms at
+//              M = 500, 46 % of it the other CTAs waiting for the panel.
+// Panel (CTA 0, one matrix row per thread in registers): the pivot of column j is the first entry of largest magnitude
+// (LAPACK idamax); rows are NOT moved -- every thread tracks the logical row number of the data it holds, a swap
+// exchanges two numbers -- so a column costs one arg-max (warp shuffles + 16 shared words), one broadcast of the pivot
+// row through shared memory and two block barriers.  The other columns of the swapped rows are gathered once per panel
+// (composition of the panel's 16 swaps), fused with U12 = L11^-1 N12.
 // =========================================================================================================
 constexpr int LU_NB = 16;
-constexpr int LU_THREADS = 1024;
-constexpr int LU_TR = 64, LU_TC = 128;   // tile of the product kernels: 64 rows x 128 columns, 2 x 4 outputs per thread
+constexpr int LU_THREADS = 512;
+constexpr int LU_TR = 64, LU_TC = 128;   // tile of the product kernels: 64 rows x 128 columns, 4 x 4 outputs per thread
+constexpr int LU_MAX_M = 4 * LU_THREADS;
 
 struct lu_args {
     const double* G; int64_t ldg; const double* Kc; int M; int D;
@@ -229,69 +238,59 @@ struct lu_args {
     double* AB; double* N; int ldn; int* piv; double* C; int* info; const int* done;
 };
 
-// Cd[i][j] (rows x cols, ld ldc) = (acc ? Cd : 0) + sign * sum_{c<K} P[i][c] Q[c][j], tiles dealt round-robin to the CTAs
-__device__ void lu_tile_product(double* Cd, int ldc, const double* P, int ldp, const double* Q, int ldq, int rows,
-                                int cols, int K, double sign, bool acc, double (*Ps)[LU_NB + 1], double (*Qs)[LU_TC]) {
+// one 64 x 128 tile: Cd[i][j] = (acc ? Cd : 0) + sign * sum_{c<K} P[i][c] Q[c][j]
+__device__ __forceinline__ void lu_tile(double* Cd, int ldc, const double* P, int ldp, const double* Q, int ldq, int rows,
+                                        int cols, int K, double sign, bool acc, int i0, int j0,
+                                        double (*Ps)[LU_NB + 1], double (*Qs)[LU_TC]) {
     const int tid = threadIdx.x;
-    const int ntr = (rows + LU_TR - 1) / LU_TR, ntc = (cols + LU_TC - 1) / LU_TC;
-    const int ty = tid >> 5, tx = tid & 31;      // 32 x 32 threads: rows ty, ty + 32; columns tx + 32 v
-    for (int tile = blockIdx.x; tile < ntr * ntc; tile += gridDim.x) {
-        const int i0 = (tile / ntc) * LU_TR, j0 = (tile % ntc) * LU_TC;
-        double s[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
-        for (int c0 = 0; c0 < K; c0 += LU_NB) {
-            __syncthreads();
-            {   // P tile: 64 x 16 = 1024 entries, one per thread
-                const int r = tid >> 4, c = tid & 15;
-                Ps[r][c] = (i0 + r < rows && c0 + c < K) ? P[(int64_t)(i0 + r) * ldp + c0 + c] : 0.0;
-            }
-            for (int e = tid; e < LU_NB * LU_TC; e += LU_THREADS) {
-                const int c = e / LU_TC, j = e % LU_TC;
-                Qs[c][j] = (c0 + c < K && j0 + j < cols) ? Q[(int64_t)(c0 + c) * ldq + j0 + j] : 0.0;
-            }
-            __syncthreads();
+    const int ty = tid >> 5, tx = tid & 31;      // 16 x 32 threads: rows ty + 16 u, columns tx + 32 v
+    double s[4][4];
 #pragma unroll
-            for (int c = 0; c < LU_NB; ++c) {
-                const double p0 = Ps[ty][c], p1 = Ps[ty + 32][c];
+    for (int u = 0; u < 4; ++u)
 #pragma unroll
-                for (int v = 0; v < 4; ++v) {
-                    const double q = Qs[c][tx + 32 * v];
-                    s[0][v] = fma(p0, q, s[0][v]);
-                    s[1][v] = fma(p1, q, s[1][v]);
-                }
+        for (int v = 0; v < 4; ++v) s[u][v] = 0.0;
+    for (int c0 = 0; c0 < K; c0 += LU_NB) {
+        __syncthreads();
+        for (int e = tid; e < LU_TR * LU_NB; e += LU_THREADS) {
+            const int r = e >> 4, c = e & 15;
+            Ps[r][c] = (i0 + r < rows && c0 + c < K) ? P[(int64_t)(i0 + r) * ldp + c0 + c] : 0.0;
+        }
+        for (int e = tid; e < LU_NB * LU_TC; e += LU_THREADS) {
+            const int c = e / LU_TC, j = e % LU_TC;
+            Qs[c][j] = (c0 + c < K && j0 + j < cols) ? Q[(int64_t)(c0 + c) * ldq + j0 + j] : 0.0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int c = 0; c < LU_NB; ++c) {
+            double pv[4], qv[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) pv[u] = Ps[ty + 16 * u][c];
+#pragma unroll
+            for (int v = 0; v < 4; ++v) qv[v] = Qs[c][tx + 32 * v];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int v = 0; v < 4; ++v) s[u][v] = fma(pv[u], qv[v], s[u][v]);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+            const int i = i0 + ty + 16 * u, j = j0 + tx + 32 * v;
+            if (i < rows && j < cols) {
+                double* dst = Cd + (int64_t)i * ldc + j;
+                *dst = acc ? fma(sign, s[u][v], *dst) : sign * s[u][v];
             }
         }
-#pragma unroll
-        for (int u = 0; u < 2; ++u)
-#pragma unroll
-            for (int v = 0; v < 4; ++v) {
-                const int i = i0 + ty + 32 * u, j = j0 + tx + 32 * v;
-                if (i < rows && j < cols) {
-                    double* dst = Cd + (int64_t)i * ldc + j;
-                    *dst = acc ? fma(sign, s[u][v], *dst) : sign * s[u][v];
-                }
-            }
-    }
 }
 
-template <int R>
-__global__ void __launch_bounds__(LU_THREADS) k_lu_solve(lu_args a) {
-    cg::grid_group grid = cg::this_grid();
+// AB = [lhs | rhs], lhs symmetric from the lower triangle of G
+__global__ void __launch_bounds__(256) k_lu_prep(lu_args a) {
     if (a.done && *a.done) return;
-    __shared__ double Ps[LU_TR][LU_NB + 1];
-    __shared__ double Qs[LU_NB][LU_TC];
-    __shared__ double rowP[LU_NB], rowJ[LU_NB];
-    __shared__ double wval[32];
-    __shared__ int widx[32];
-    __shared__ int s_piv;
-    const int M = a.M, D = a.D, W = a.M + a.D, ldn = a.ldn;
-    const int tid = threadIdx.x;
-    const int64_t gtid = (int64_t)blockIdx.x * LU_THREADS + tid, gsz = (int64_t)gridDim.x * LU_THREADS;
+    const int M = a.M, W = a.M + a.D;
     const double ls = a.lam_sigma2_ptr ? *a.lam_sigma2_ptr : a.lam_sigma2;
-    double* AB = a.AB;
-    double* N = a.N;
-
-    // phase 0: AB = [lhs | rhs], lhs symmetric from the lower triangle of G
-    for (int64_t e = gtid; e < (int64_t)M * W; e += gsz) {
+    for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < (int64_t)M * W; e += (int64_t)gridDim.x * 256) {
         const int i = (int)(e / W), j = (int)(e % W);
         double v;
         if (j >= M) v = a.G[(int64_t)j * a.ldg + i];                       // rhs[i][d] = G[M + d][i]
@@ -299,146 +298,175 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_solve(lu_args a) {
             const int hi = i > j ? i : j, lo = i > j ? j : i;
             v = a.G[(int64_t)hi * a.ldg + lo] + ls * a.Kc[(int64_t)i * M + j];
         }
-        AB[(int64_t)i * ldn + j] = v;
+        a.AB[(int64_t)i * a.ldn + j] = v;
     }
-    grid.sync();
-    // phase 1: N = lhs [lhs | rhs]
-    lu_tile_product(N, ldn, AB, ldn, AB, ldn, M, W, M, 1.0, false, Ps, Qs);
-    grid.sync();
+}
 
-    // phase 2: LU with partial pivoting
+// N = lhs [lhs | rhs]: one 64 x 128 tile per CTA
+__global__ void __launch_bounds__(LU_THREADS) k_lu_ata(lu_args a) {
+    if (a.done && *a.done) return;
+    __shared__ double Ps[LU_TR][LU_NB + 1];
+    __shared__ double Qs[LU_NB][LU_TC];
+    const int W = a.M + a.D, ntc = (W + LU_TC - 1) / LU_TC;
+    lu_tile(a.N, a.ldn, a.AB, a.ldn, a.AB, a.ldn, a.M, W, a.M, 1.0, false, (blockIdx.x / ntc) * LU_TR,
+            (blockIdx.x % ntc) * LU_TC, Ps, Qs);
+}
+
+__device__ __forceinline__ void lu_argmax_step(double& bv, int& bp, int& bo, int o) {
+    const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int op = __shfl_xor_sync(0xffffffffu, bp, o);
+    const int oo = __shfl_xor_sync(0xffffffffu, bo, o);
+    if (ov > bv || (ov == bv && op < bp)) { bv = ov; bp = op; bo = oo; }
+}
+
+template <int R>
+__global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
+    cg::cluster_group cluster = cg::this_cluster();
+    if (a.done && *a.done) return;               // uniform over the cluster
+    __shared__ double Ps[LU_TR][LU_NB + 1];
+    __shared__ double Qs[LU_NB][LU_TC];
+    __shared__ double rowP[2][LU_NB];
+    __shared__ double wval[2][LU_THREADS / 32];
+    __shared__ int wpos[2][LU_THREADS / 32], wown[2][LU_THREADS / 32];
+    __shared__ int s_piv[LU_NB];
+    __shared__ int s_tp[2 * LU_NB], s_ts[2 * LU_NB], s_np;
+    const int M = a.M, D = a.D, W = a.M + a.D, ldn = a.ldn;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int crank = (int)cluster.block_rank(), csize = (int)cluster.num_blocks();
+    double* N = a.N;
+    constexpr int NOROW = 0x7fffffff;
+
     for (int k0 = 0; k0 < M; k0 += LU_NB) {
         const int nbe = min(LU_NB, M - k0);
-        if (blockIdx.x == 0) {
+        // ---- (a) panel factorisation, CTA 0 ----
+        if (crank == 0) {
             double av[R][LU_NB];
+            int pos[R];
 #pragma unroll
             for (int q = 0; q < R; ++q) {
                 const int r = k0 + tid + LU_THREADS * q;
+                pos[q] = r < M ? r : NOROW;
 #pragma unroll
                 for (int c = 0; c < LU_NB; ++c) av[q][c] = (r < M && c < nbe) ? N[(int64_t)r * ldn + k0 + c] : 0.0;
             }
 #pragma unroll
             for (int j = 0; j < LU_NB; ++j) {
                 if (j < nbe) {                     // uniform over the CTA
-                    // pivot: first row >= k0 + j with the largest |entry| in column j
+                    const int par = j & 1;
                     double bv = -1.0;
-                    int bi = 0x7fffffff;
+                    int bp = NOROW, bo = 0;
 #pragma unroll
                     for (int q = 0; q < R; ++q) {
-                        const int r = k0 + tid + LU_THREADS * q;
                         const double v = fabs(av[q][j]);
-                        if (r < M && r >= k0 + j && (v > bv)) { bv = v; bi = r; }
-                    }
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) {
-                        const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-                        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-                        if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
-                    }
-                    if ((tid & 31) == 0) { wval[tid >> 5] = bv; widx[tid >> 5] = bi; }
-                    __syncthreads();
-                    if (tid < 32) {
-                        bv = wval[tid]; bi = widx[tid];
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) {
-                            const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-                            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-                            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
-                        }
-                        if (tid == 0) {
-                            s_piv = bi;
-                            a.piv[j] = bi;
-                            if (!(bv > 0.0)) atomicCAS(a.info, 0, k0 + j + 1);      // exactly singular (or NaN)
+                        if (pos[q] != NOROW && pos[q] >= k0 + j && (v > bv || (v == bv && pos[q] < bp))) {
+                            bv = v; bp = pos[q]; bo = tid * R + q;
                         }
                     }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) lu_argmax_step(bv, bp, bo, o);
+                    if (lane == 0) { wval[par][warp] = bv; wpos[par][warp] = bp; wown[par][warp] = bo; }
                     __syncthreads();
-                    const int p = s_piv;
+                    {   // every warp reduces the 16 warp candidates itself (no second barrier)
+                        const int w = lane & (LU_THREADS / 32 - 1);
+                        bv = wval[par][w]; bp = wpos[par][w]; bo = wown[par][w];
+#pragma unroll
+                        for (int o = 8; o > 0; o >>= 1) lu_argmax_step(bv, bp, bo, o);
+                    }
+                    if (tid == 0) {
+                        s_piv[j] = bp;
+                        if (!(bv > 0.0)) atomicCAS(a.info, 0, k0 + j + 1);      // exactly singular (or NaN)
+                    }
 #pragma unroll
                     for (int q = 0; q < R; ++q) {
-                        const int r = k0 + tid + LU_THREADS * q;
-                        if (r == p) {
+                        if (tid * R + q == bo) {             // this thread holds the pivot row: it becomes row k0 + j
 #pragma unroll
-                            for (int c = 0; c < LU_NB; ++c) rowP[c] = av[q][c];
-                        }
-                        if (r == k0 + j) {
-#pragma unroll
-                            for (int c = 0; c < LU_NB; ++c) rowJ[c] = av[q][c];
+                            for (int c = 0; c < LU_NB; ++c) rowP[par][c] = av[q][c];
+                            pos[q] = k0 + j;
+                        } else if (pos[q] == k0 + j) {
+                            pos[q] = bp;                     // the row that sat at k0 + j goes where the pivot row was
                         }
                     }
                     __syncthreads();
-                    const double pv = rowP[j];
+                    const double pv = rowP[par][j];
 #pragma unroll
                     for (int q = 0; q < R; ++q) {
-                        const int r = k0 + tid + LU_THREADS * q;
-                        if (r == k0 + j) {
-#pragma unroll
-                            for (int c = 0; c < LU_NB; ++c) av[q][c] = rowP[c];
-                        } else if (r == p) {
-#pragma unroll
-                            for (int c = 0; c < LU_NB; ++c) av[q][c] = rowJ[c];
-                        }
-                        if (r > k0 + j && r < M) {
+                        if (pos[q] != NOROW && pos[q] > k0 + j) {
                             const double l = av[q][j] / pv;
                             av[q][j] = l;
 #pragma unroll
                             for (int c = 0; c < LU_NB; ++c)
-                                if (c > j) av[q][c] = fma(-l, rowP[c], av[q][c]);
+                                if (c > j) av[q][c] = fma(-l, rowP[par][c], av[q][c]);
                         }
                     }
-                    __syncthreads();
                 }
             }
 #pragma unroll
             for (int q = 0; q < R; ++q) {
-                const int r = k0 + tid + LU_THREADS * q;
-                if (r < M) {
+                if (pos[q] != NOROW) {
 #pragma unroll
                     for (int c = 0; c < LU_NB; ++c)
-                        if (c < nbe) N[(int64_t)r * ldn + k0 + c] = av[q][c];
+                        if (c < nbe) N[(int64_t)pos[q] * ldn + k0 + c] = av[q][c];
                 }
             }
+            __syncthreads();
+            if (tid < nbe) a.piv[tid] = s_piv[tid];
         }
-        grid.sync();
-        // row swaps of the columns to the right of the panel (incl. the right-hand sides), then U12 = L11^-1 N12
+        cluster.sync();
+        // ---- (b) the panel's row swaps applied to the columns right of it (incl. the right-hand sides), fused with
+        //      U12 = L11^-1 N12.  The 16 swaps are composed first: position tp[i] receives the old row ts[i]. ----
         {
             double (*L11)[LU_NB + 1] = Ps;
             if (tid < LU_NB * LU_NB) {
                 const int i = tid / LU_NB, j = tid % LU_NB;
                 L11[i][j] = (i < nbe && j < i) ? N[(int64_t)(k0 + i) * ldn + k0 + j] : 0.0;
             }
+            if (tid == 0) {
+                int np = nbe;
+                for (int i = 0; i < nbe; ++i) { s_tp[i] = k0 + i; s_ts[i] = k0 + i; }
+                for (int j = 0; j < nbe; ++j) {
+                    const int p = a.piv[j];
+                    int b = -1;
+                    for (int i = 0; i < np; ++i)
+                        if (s_tp[i] == p) b = i;
+                    if (b < 0) { b = np++; s_tp[b] = p; s_ts[b] = p; }
+                    const int t = s_ts[j]; s_ts[j] = s_ts[b]; s_ts[b] = t;
+                }
+                s_np = np;
+            }
             __syncthreads();
-            for (int64_t cc = k0 + nbe + gtid; cc < W; cc += gsz) {
-                double u[LU_NB];
+            const int np = s_np;
+            for (int cc = k0 + nbe + crank * LU_THREADS + tid; cc < W; cc += csize * LU_THREADS) {
+                double vals[2 * LU_NB];
+#pragma unroll
+                for (int i = 0; i < 2 * LU_NB; ++i) vals[i] = (i < np) ? N[(int64_t)s_ts[i] * ldn + cc] : 0.0;
 #pragma unroll
                 for (int j = 0; j < LU_NB; ++j) {
-                    if (j < nbe) {
-                        const int p = a.piv[j];
-                        double* x = N + (int64_t)(k0 + j) * ldn + cc;
-                        if (p != k0 + j) {
-                            double* y = N + (int64_t)p * ldn + cc;
-                            const double t = *x; *x = *y; *y = t;
-                        }
-                        double s = *x;
+                    double s = vals[j];
 #pragma unroll
-                        for (int i = 0; i < LU_NB; ++i)
-                            if (i < j) s = fma(-L11[j][i], u[i], s);
-                        u[j] = s;
-                        *x = s;
-                    }
+                    for (int i = 0; i < LU_NB; ++i)
+                        if (i < j) s = fma(-L11[j][i], vals[i], s);
+                    vals[j] = s;
                 }
+#pragma unroll
+                for (int i = 0; i < 2 * LU_NB; ++i)
+                    if (i < np) N[(int64_t)s_tp[i] * ldn + cc] = vals[i];
             }
         }
-        grid.sync();
-        // trailing update N22 -= L21 U12
+        cluster.sync();
+        // ---- (c) trailing update N22 -= L21 U12 ----
         const int r0 = k0 + nbe;
-        if (r0 < M)
-            lu_tile_product(N + (int64_t)r0 * ldn + r0, ldn, N + (int64_t)r0 * ldn + k0, ldn, N + (int64_t)k0 * ldn + r0, ldn,
-                            M - r0, W - r0, nbe, -1.0, true, Ps, Qs);
-        grid.sync();
+        if (r0 < M) {
+            const int rows = M - r0, cols = W - r0;
+            const int ntr = (rows + LU_TR - 1) / LU_TR, ntc = (cols + LU_TC - 1) / LU_TC;
+            for (int tile = crank; tile < ntr * ntc; tile += csize)
+                lu_tile(N + (int64_t)r0 * ldn + r0, ldn, N + (int64_t)r0 * ldn + k0, ldn, N + (int64_t)k0 * ldn + r0, ldn,
+                        rows, cols, nbe, -1.0, true, (tile / ntc) * LU_TR, (tile % ntc) * LU_TC, Ps, Qs);
+        }
+        cluster.sync();
     }
 
-    // phase 3: back substitution U X = Y (Y = columns M .. M+D-1 of N), CTA 0
-    if (blockIdx.x != 0) return;
+    // ---- back substitution U X = Y (Y = columns M .. M+D-1 of N), CTA 0 ----
+    if (crank != 0) return;
     double (*Ub)[LU_NB + 1] = Ps;                   // U block, 16 x 16
     double (*Xb)[LU_TC] = Qs;                       // solved block rows, 16 x D   (D <= 64 < LU_TC)
     const int nblk = (M + LU_NB - 1) / LU_NB;
@@ -467,6 +495,7 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_solve(lu_args a) {
             const int i = e / D, d = e % D;
             double s = N[(int64_t)i * ldn + M + d];
             const double* urow = N + (int64_t)i * ldn + k0;
+#pragma unroll 4
             for (int j = 0; j < nbe; ++j) s = fma(-urow[j], Xb[j][d], s);
             N[(int64_t)i * ldn + M + d] = s;
         }
@@ -479,10 +508,42 @@ size_t solve_normal_ws_bytes(int M, int D) {
     return sizeof(double) * 2 * (size_t)M * lu_ldn(M, D) + 256;
 }
 
+template <int R>
+static int lu_launch_factor(const lu_args& a, cudaStream_t st) {
+    static int cluster_size = 0;
+    if (!cluster_size) {
+        DVF_CUDA(cudaFuncSetAttribute(k_lu_factor<R>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        for (int cs : {16, 8, 4, 2, 1}) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(cs); cfg.blockDim = dim3(LU_THREADS);
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, k_lu_factor<R>, &cfg) == cudaSuccess && n >= 1) { cluster_size = cs; break; }
+            cudaGetLastError();
+        }
+        if (!cluster_size) { set_error("k_lu_factor cannot be scheduled"); return DVF_ERR_CUDA; }
+        static const char* force = getenv("DVF_LU_CLUSTER");   // developer knob
+        if (force && atoi(force) > 0 && atoi(force) <= cluster_size) cluster_size = atoi(force);
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cluster_size); cfg.blockDim = dim3(LU_THREADS); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cluster_size; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    ++g_launch_count;
+    DVF_CUDA(cudaLaunchKernelEx(&cfg, k_lu_factor<R>, a));
+    return DVF_OK;
+}
+
 int solve_normal_run(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
                      const double* lam_sigma2_ptr, void* ws, double* C, int* info, const int* done, cudaStream_t st) {
-    if (M > 4 * LU_THREADS) {
-        set_error("lstsq_method='drouin' (normal equations + LU) supports M <= %d control points; M = %d", 4 * LU_THREADS, M);
+    if (M > LU_MAX_M) {
+        set_error("lstsq_method='drouin' (normal equations + LU) supports M <= %d control points; M = %d (use "
+                  "lstsq_method='cholesky')", LU_MAX_M, M);
         return DVF_ERR_ARG;
     }
     const int ldn = lu_ldn(M, D);
@@ -490,25 +551,16 @@ int solve_normal_run(const double* G, int64_t ldg, const double* Kc, int M, int 
     double* N = AB + (size_t)M * ldn;
     int* piv = (int*)(N + (size_t)M * ldn);
     lu_args a{G, ldg, Kc, M, D, lam_sigma2, lam_sigma2_ptr, AB, N, ldn, piv, C, info, done};
-    const void* fn = M <= LU_THREADS ? (const void*)k_lu_solve<1>
-                     : (M <= 2 * LU_THREADS ? (const void*)k_lu_solve<2> : (const void*)k_lu_solve<4>);
-    static int resident[3] = {-1, -1, -1};
-    const int slot = M <= LU_THREADS ? 0 : (M <= 2 * LU_THREADS ? 1 : 2);
-    if (resident[slot] < 0) {
-        int per_sm = 0;
-        DVF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, LU_THREADS, 0));
-        resident[slot] = per_sm > 0 ? num_sms() : 0;
-    }
-    if (resident[slot] == 0) { set_error("k_lu_solve cannot be made resident"); return DVF_ERR_CUDA; }
-    int grid = ((M + LU_TR - 1) / LU_TR) * ((M + D + LU_TC - 1) / LU_TC);
-    if (grid < 8) grid = 8;
-    if (grid > resident[slot]) grid = resident[slot];
-    static const char* force = getenv("DVF_SOLVE_GRID");
-    if (force && atoi(force) > 0) grid = std::min(atoi(force), resident[slot]);
-    void* params[] = {&a};
-    ++g_launch_count;
-    DVF_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(LU_THREADS), params, 0, st));
-    return DVF_OK;
+    const int W = M + D;
+    int nb = (int)(((int64_t)M * W + 255) / 256);
+    if (nb > 4 * num_sms()) nb = 4 * num_sms();
+    k_lu_prep<<<nb, 256, 0, st>>>(a);
+    DVF_LAUNCH_CHECK();
+    k_lu_ata<<<((M + LU_TR - 1) / LU_TR) * ((W + LU_TC - 1) / LU_TC), LU_THREADS, 0, st>>>(a);
+    DVF_LAUNCH_CHECK();
+    if (M <= LU_THREADS) return lu_launch_factor<1>(a, st);
+    if (M <= 2 * LU_THREADS) return lu_launch_factor<2>(a, st);
+    return lu_launch_factor<4>(a, st);
 }
 
 }  // namespace dvf

@@ -194,6 +194,16 @@ def bandwidth(ctrl) -> float:
     c = torch.as_tensor(ctrl, dtype=torch.float64)
     n = c.shape[0]
     k = max(2, int(0.2 * n)) - 1
+    if c.is_cuda and n <= 16384:
+        # one kernel: distances + sort per control point (kern_post.cu, k_knn_dists)
+        from . import _lib
+        from .device import stream_ptr
+        kk = min(k + 1, n)
+        c = c.contiguous()
+        out = torch.empty((n, kk), dtype=torch.float64, device=c.device)
+        _lib.check(_lib.load().dvf_knn_dists(c.data_ptr(), n, c.shape[1], kk, out.data_ptr(), stream_ptr()))
+        part = out.cpu().numpy()
+        return float(np.sqrt(2) * (np.mean(part[:, 1:]) / 1.5))
     ct = c.T.contiguous()
     d2 = torch.zeros((n, n), dtype=torch.float64, device=c.device)
     diff = torch.empty_like(d2)

@@ -110,6 +110,10 @@ int dvf_vector_transform(const double* V, int64_t n, int D, const double* Q, int
 int dvf_jacobian_det(const double* J, int64_t n, int D, double* det, void* stream);
 int dvf_cell_angles(const double* U, const double* V, int64_t n, int D, double* out, void* stream);
 int dvf_row_norms(const double* V, int64_t n, int D, double* out, void* stream);
+/* bandwidth_selector's neighbour search (scVectorField.py:121-135 -> tools/connectivity.py:565-577, exact kNN): out
+ * (M x kk, row-major) = Euclidean distances from control point i to its kk nearest control points, itself included,
+ * ascending.  Squared distances are summed dimension by dimension with separate multiply / add (sklearn's order). */
+int dvf_knn_dists(const double* Xc, int M, int D, int kk, double* out, void* stream);
 
 /* ---- K10: second derivatives of the field ----------------------------------------------------
  * dvf_hessian: H[c][i][l][m] = d^2 f_i / dx_l dx_m at x_c  (n x D x D x D, cell-major).  replaces

@@ -59,7 +59,10 @@ def main():
             rels = {k: float(np.max(np.abs(got[k] - one[k])) / np.max(np.abs(one[k]))) for k in
                     ("V", "C", "P", "E_traj", "tecr_traj")}
             rels["sigma2"] = abs(got["sigma2"] - one["sigma2"]) / one["sigma2"]
-            good = same_keys and exact and all(v < 1e-10 for k, v in rels.items() if k != "tecr_traj")
+            # the sharded Gram sums in a different order (1e-16); the normal-equations form amplifies that by cond(lhs)^2
+            # in C (6e-9 here, like the reference against itself), Cholesky by cond(lhs)
+            tol = {"C": 1e-7 if method == "drouin" else 1e-10}
+            good = same_keys and exact and all(v < tol.get(k, 1e-10) for k, v in rels.items() if k != "tecr_traj")
             print("world=%d API dict (%s): keys equal %s, index/identity fields exact %s, rel %s -> %s"
                   % (world, method, same_keys, exact, {k: "%.2g" % v for k, v in rels.items()}, "ok" if good else "FAIL"),
                   flush=True)

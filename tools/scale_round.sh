@@ -17,7 +17,7 @@ $B --gpus $N --steps 2 --warmup 2 --workload c5 --no-cpu-baseline --no-e2e > gpu
 for f in weak_c3 strong_c3 strong_c5; do python - <<PY
 import json
 try:
-    d = json.load(open("gpurun_out/${TAG}_${f}_n$N.json"))
+    d = json.loads([l for l in open("gpurun_out/${TAG}_${f}_n$N.json").read().splitlines() if l.startswith("{")][-1])
     print("${f} n=$N value %.4g ms %.1f stages %s e2e %s iters %s" % (d["value"], d["ms_per_step"], {k: round(v, 1) for k, v in d["stages_ms"].items()}, d["e2e"] and round(d["e2e"]["value"]), d["config"]["em_iterations"]))
     if "parity_vs_1gpu" in d: print("   parity_vs_1gpu:", json.dumps(d["parity_vs_1gpu"]))
 except Exception as e:
