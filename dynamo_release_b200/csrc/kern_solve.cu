@@ -229,8 +229,10 @@ namespace dvf {
 // =========================================================================================================
 constexpr int LU_NB = 16;
 constexpr int LU_THREADS = 512;
-constexpr int LU_TR = 64, LU_TC = 128;   // tile of the product kernels: 64 rows x 128 columns, 4 x 4 outputs per thread
-constexpr int LU_MAX_M = 4 * LU_THREADS;
+constexpr int LU_TR = 64, LU_TC = 128;   // tile of the trailing update: 64 rows x 128 columns, 4 x 4 outputs per thread
+constexpr int LU_ATR = 32, LU_ATC = 64;  // tile of N = lhs [lhs | rhs]: small, so that M = 500 already fills the GPU (144 CTAs)
+constexpr int LU_PWMAX = 16;             // at most all warps of CTA 0 factor the panel (named barrier 1), R rows per thread
+constexpr int LU_MAX_M = 4 * LU_PWMAX * 32;
 
 struct lu_args {
     const double* G; int64_t ldg; const double* Kc; int M; int D;
@@ -238,45 +240,48 @@ struct lu_args {
     double* AB; double* N; int ldn; int* piv; double* C; int* info; const int* done;
 };
 
-// one 64 x 128 tile: Cd[i][j] = (acc ? Cd : 0) + sign * sum_{c<K} P[i][c] Q[c][j]
+// one TR x TC tile (512 threads, 16 x 32; TR / 16 x TC / 32 outputs per thread):
+//   Cd[i][j] = (acc ? Cd : 0) + sign * sum_{c<K} P[i][c] Q[c][j]
+template <int TR, int TC>
 __device__ __forceinline__ void lu_tile(double* Cd, int ldc, const double* P, int ldp, const double* Q, int ldq, int rows,
                                         int cols, int K, double sign, bool acc, int i0, int j0,
-                                        double (*Ps)[LU_NB + 1], double (*Qs)[LU_TC]) {
+                                        double (*Ps)[LU_NB + 1], double (*Qs)[TC]) {
+    constexpr int RU = TR / 16, CV = TC / 32;
     const int tid = threadIdx.x;
-    const int ty = tid >> 5, tx = tid & 31;      // 16 x 32 threads: rows ty + 16 u, columns tx + 32 v
-    double s[4][4];
+    const int ty = tid >> 5, tx = tid & 31;      // rows ty + 16 u, columns tx + 32 v
+    double s[RU][CV];
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < RU; ++u)
 #pragma unroll
-        for (int v = 0; v < 4; ++v) s[u][v] = 0.0;
+        for (int v = 0; v < CV; ++v) s[u][v] = 0.0;
     for (int c0 = 0; c0 < K; c0 += LU_NB) {
         __syncthreads();
-        for (int e = tid; e < LU_TR * LU_NB; e += LU_THREADS) {
+        for (int e = tid; e < TR * LU_NB; e += LU_THREADS) {
             const int r = e >> 4, c = e & 15;
             Ps[r][c] = (i0 + r < rows && c0 + c < K) ? P[(int64_t)(i0 + r) * ldp + c0 + c] : 0.0;
         }
-        for (int e = tid; e < LU_NB * LU_TC; e += LU_THREADS) {
-            const int c = e / LU_TC, j = e % LU_TC;
+        for (int e = tid; e < LU_NB * TC; e += LU_THREADS) {
+            const int c = e / TC, j = e % TC;
             Qs[c][j] = (c0 + c < K && j0 + j < cols) ? Q[(int64_t)(c0 + c) * ldq + j0 + j] : 0.0;
         }
         __syncthreads();
 #pragma unroll
         for (int c = 0; c < LU_NB; ++c) {
-            double pv[4], qv[4];
+            double pv[RU], qv[CV];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) pv[u] = Ps[ty + 16 * u][c];
+            for (int u = 0; u < RU; ++u) pv[u] = Ps[ty + 16 * u][c];
 #pragma unroll
-            for (int v = 0; v < 4; ++v) qv[v] = Qs[c][tx + 32 * v];
+            for (int v = 0; v < CV; ++v) qv[v] = Qs[c][tx + 32 * v];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < RU; ++u)
 #pragma unroll
-                for (int v = 0; v < 4; ++v) s[u][v] = fma(pv[u], qv[v], s[u][v]);
+                for (int v = 0; v < CV; ++v) s[u][v] = fma(pv[u], qv[v], s[u][v]);
         }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
+    for (int u = 0; u < RU; ++u)
 #pragma unroll
-        for (int v = 0; v < 4; ++v) {
+        for (int v = 0; v < CV; ++v) {
             const int i = i0 + ty + 16 * u, j = j0 + tx + 32 * v;
             if (i < rows && j < cols) {
                 double* dst = Cd + (int64_t)i * ldc + j;
@@ -302,32 +307,42 @@ __global__ void __launch_bounds__(256) k_lu_prep(lu_args a) {
     }
 }
 
-// N = lhs [lhs | rhs]: one 64 x 128 tile per CTA
+// N = lhs [lhs | rhs]: one 32 x 64 tile per CTA
 __global__ void __launch_bounds__(LU_THREADS) k_lu_ata(lu_args a) {
     if (a.done && *a.done) return;
-    __shared__ double Ps[LU_TR][LU_NB + 1];
-    __shared__ double Qs[LU_NB][LU_TC];
-    const int W = a.M + a.D, ntc = (W + LU_TC - 1) / LU_TC;
-    lu_tile(a.N, a.ldn, a.AB, a.ldn, a.AB, a.ldn, a.M, W, a.M, 1.0, false, (blockIdx.x / ntc) * LU_TR,
-            (blockIdx.x % ntc) * LU_TC, Ps, Qs);
+    __shared__ double Ps[LU_ATR][LU_NB + 1];
+    __shared__ double Qs[LU_NB][LU_ATC];
+    const int W = a.M + a.D, ntc = (W + LU_ATC - 1) / LU_ATC;
+    lu_tile<LU_ATR, LU_ATC>(a.N, a.ldn, a.AB, a.ldn, a.AB, a.ldn, a.M, W, a.M, 1.0, false, (blockIdx.x / ntc) * LU_ATR,
+                            (blockIdx.x % ntc) * LU_ATC, Ps, Qs);
 }
 
-__device__ __forceinline__ void lu_argmax_step(double& bv, int& bp, int& bo, int o) {
-    const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-    const int op = __shfl_xor_sync(0xffffffffu, bp, o);
-    const int oo = __shfl_xor_sync(0xffffffffu, bo, o);
-    if (ov > bv || (ov == bv && op < bp)) { bv = ov; bp = op; bo = oo; }
+__device__ __forceinline__ unsigned long long lu_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
+// phase timers of CTA 0 (ns, accumulated over the panels), kept behind the pivot array in the workspace: developer
+// aid for tools/solve_tune.py, a handful of timer reads per panel
+#define LU_MARK(slot)                                                    \
+    do {                                                                 \
+        if (tid == 0 && crank == 0) {                                    \
+            const unsigned long long now__ = lu_now();                   \
+            tacc[slot] += now__ - tlast;                                 \
+            tlast = now__;                                               \
+        }                                                                \
+    } while (0)
 
-template <int R>
+template <int R, int LU_PW>
 __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
     cg::cluster_group cluster = cg::this_cluster();
     if (a.done && *a.done) return;               // uniform over the cluster
+    unsigned long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = lu_now();
     __shared__ double Ps[LU_TR][LU_NB + 1];
     __shared__ double Qs[LU_NB][LU_TC];
     __shared__ double rowP[2][LU_NB];
-    __shared__ double wval[2][LU_THREADS / 32];
-    __shared__ int wpos[2][LU_THREADS / 32], wown[2][LU_THREADS / 32];
+    __shared__ double wval[2][LU_PWMAX], wsgn[2][LU_PWMAX];
+    __shared__ int wpos[2][LU_PWMAX], wown[2][LU_PWMAX];
     __shared__ int s_piv[LU_NB];
     __shared__ int s_tp[2 * LU_NB], s_ts[2 * LU_NB], s_np;
     const int M = a.M, D = a.D, W = a.M + a.D, ldn = a.ldn;
@@ -338,40 +353,59 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
 
     for (int k0 = 0; k0 < M; k0 += LU_NB) {
         const int nbe = min(LU_NB, M - k0);
-        // ---- (a) panel factorisation, CTA 0 ----
-        if (crank == 0) {
+        // ---- (a) panel factorisation: the first LU_PW warps of CTA 0, R rows per thread, named barrier 1 ----
+        if (crank == 0 && warp < LU_PW) {
+            constexpr int PT = LU_PW * 32;
             double av[R][LU_NB];
             int pos[R];
 #pragma unroll
             for (int q = 0; q < R; ++q) {
-                const int r = k0 + tid + LU_THREADS * q;
+                const int r = k0 + tid + PT * q;
                 pos[q] = r < M ? r : NOROW;
 #pragma unroll
                 for (int c = 0; c < LU_NB; ++c) av[q][c] = (r < M && c < nbe) ? N[(int64_t)r * ldn + k0 + c] : 0.0;
             }
 #pragma unroll
             for (int j = 0; j < LU_NB; ++j) {
-                if (j < nbe) {                     // uniform over the CTA
+                if (j < nbe) {                     // uniform over the panel warps
                     const int par = j & 1;
-                    double bv = -1.0;
+                    // arg-max of |column j| over the rows not yet eliminated: the magnitude first (5 shuffles), then the
+                    // smallest logical row among the lanes that hold it (one ballot unless magnitudes tie)
+                    double bv = -1.0, bs = 0.0;
                     int bp = NOROW, bo = 0;
 #pragma unroll
                     for (int q = 0; q < R; ++q) {
                         const double v = fabs(av[q][j]);
                         if (pos[q] != NOROW && pos[q] >= k0 + j && (v > bv || (v == bv && pos[q] < bp))) {
-                            bv = v; bp = pos[q]; bo = tid * R + q;
+                            bv = v; bs = av[q][j]; bp = pos[q]; bo = tid * R + q;
                         }
                     }
+                    double wv = bv;
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) lu_argmax_step(bv, bp, bo, o);
-                    if (lane == 0) { wval[par][warp] = bv; wpos[par][warp] = bp; wown[par][warp] = bo; }
-                    __syncthreads();
-                    {   // every warp reduces the 16 warp candidates itself (no second barrier)
-                        const int w = lane & (LU_THREADS / 32 - 1);
-                        bv = wval[par][w]; bp = wpos[par][w]; bo = wown[par][w];
+                    for (int o = 16; o > 0; o >>= 1) wv = fmax(wv, __shfl_xor_sync(0xffffffffu, wv, o));
+                    const unsigned eq = __ballot_sync(0xffffffffu, bv == wv && bp != NOROW);
+                    if (__popc(eq) > 1) {          // tie in magnitude: LAPACK's idamax takes the first row
+                        int mp = (bv == wv) ? bp : NOROW;
 #pragma unroll
-                        for (int o = 8; o > 0; o >>= 1) lu_argmax_step(bv, bp, bo, o);
+                        for (int o = 16; o > 0; o >>= 1) mp = min(mp, __shfl_xor_sync(0xffffffffu, mp, o));
+                        const unsigned eq2 = __ballot_sync(0xffffffffu, bv == wv && bp == mp);
+                        if (lane == __ffs(eq2) - 1) { wval[par][warp] = bv; wsgn[par][warp] = bs; wpos[par][warp] = bp; wown[par][warp] = bo; }
+                    } else if (eq == 0) {          // no candidate in this warp (all its rows are eliminated / NaN)
+                        if (lane == 0) { wval[par][warp] = -1.0; wsgn[par][warp] = 0.0; wpos[par][warp] = NOROW; wown[par][warp] = 0; }
+                    } else if (lane == __ffs(eq) - 1) {
+                        wval[par][warp] = bv; wsgn[par][warp] = bs; wpos[par][warp] = bp; wown[par][warp] = bo;
                     }
+                    asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
+                    bv = -1.0; bs = 0.0; bp = NOROW; bo = 0;
+#pragma unroll
+                    for (int w = 0; w < LU_PW; ++w) {   // broadcast reads; every thread scans the LU_PW candidates
+                        const double v = wval[par][w];
+                        const int p2 = wpos[par][w];
+                        if (v > bv || (v == bv && p2 < bp)) { bv = v; bs = wsgn[par][w]; bp = p2; bo = wown[par][w]; }
+                    }
+                    // LAPACK getf2 scales the column by the reciprocal of the pivot (|pivot| >= sfmin); the division
+                    // runs while the pivot row travels through shared memory
+                    const double rpv = 1.0 / bs;
                     if (tid == 0) {
                         s_piv[j] = bp;
                         if (!(bv > 0.0)) atomicCAS(a.info, 0, k0 + j + 1);      // exactly singular (or NaN)
@@ -386,12 +420,11 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
                             pos[q] = bp;                     // the row that sat at k0 + j goes where the pivot row was
                         }
                     }
-                    __syncthreads();
-                    const double pv = rowP[par][j];
+                    asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
 #pragma unroll
                     for (int q = 0; q < R; ++q) {
                         if (pos[q] != NOROW && pos[q] > k0 + j) {
-                            const double l = av[q][j] / pv;
+                            const double l = av[q][j] * rpv;
                             av[q][j] = l;
 #pragma unroll
                             for (int c = 0; c < LU_NB; ++c)
@@ -408,10 +441,12 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
                         if (c < nbe) N[(int64_t)pos[q] * ldn + k0 + c] = av[q][c];
                 }
             }
-            __syncthreads();
+            asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
             if (tid < nbe) a.piv[tid] = s_piv[tid];
         }
+        LU_MARK(0);
         cluster.sync();
+        LU_MARK(1);
         // ---- (b) the panel's row swaps applied to the columns right of it (incl. the right-hand sides), fused with
         //      U12 = L11^-1 N12.  The 16 swaps are composed first: position tp[i] receives the old row ts[i]. ----
         {
@@ -420,18 +455,22 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
                 const int i = tid / LU_NB, j = tid % LU_NB;
                 L11[i][j] = (i < nbe && j < i) ? N[(int64_t)(k0 + i) * ldn + k0 + j] : 0.0;
             }
-            if (tid == 0) {
+            if (warp == 0) {       // lane i holds touched position tp and the old row ts that ends up there
                 int np = nbe;
-                for (int i = 0; i < nbe; ++i) { s_tp[i] = k0 + i; s_ts[i] = k0 + i; }
+                int tp = lane < nbe ? k0 + lane : -1, ts = tp;
+                const int mypiv = lane < nbe ? a.piv[lane] : 0;
                 for (int j = 0; j < nbe; ++j) {
-                    const int p = a.piv[j];
-                    int b = -1;
-                    for (int i = 0; i < np; ++i)
-                        if (s_tp[i] == p) b = i;
-                    if (b < 0) { b = np++; s_tp[b] = p; s_ts[b] = p; }
-                    const int t = s_ts[j]; s_ts[j] = s_ts[b]; s_ts[b] = t;
+                    const int p = __shfl_sync(0xffffffffu, mypiv, j);
+                    const unsigned hit = __ballot_sync(0xffffffffu, lane < np && tp == p);
+                    int b;
+                    if (hit) b = __ffs(hit) - 1;
+                    else { b = np++; if (lane == b) { tp = p; ts = p; } }
+                    const int tj = __shfl_sync(0xffffffffu, ts, j), tb = __shfl_sync(0xffffffffu, ts, b);
+                    if (lane == j) ts = tb;
+                    if (lane == b) ts = tj;
                 }
-                s_np = np;
+                s_tp[lane] = tp; s_ts[lane] = ts;
+                if (lane == 0) s_np = np;
             }
             __syncthreads();
             const int np = s_np;
@@ -452,67 +491,133 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
                     if (i < np) N[(int64_t)s_tp[i] * ldn + cc] = vals[i];
             }
         }
+        LU_MARK(2);
         cluster.sync();
+        LU_MARK(3);
         // ---- (c) trailing update N22 -= L21 U12 ----
         const int r0 = k0 + nbe;
         if (r0 < M) {
             const int rows = M - r0, cols = W - r0;
             const int ntr = (rows + LU_TR - 1) / LU_TR, ntc = (cols + LU_TC - 1) / LU_TC;
             for (int tile = crank; tile < ntr * ntc; tile += csize)
-                lu_tile(N + (int64_t)r0 * ldn + r0, ldn, N + (int64_t)r0 * ldn + k0, ldn, N + (int64_t)k0 * ldn + r0, ldn,
-                        rows, cols, nbe, -1.0, true, (tile / ntc) * LU_TR, (tile % ntc) * LU_TC, Ps, Qs);
+                lu_tile<LU_TR, LU_TC>(N + (int64_t)r0 * ldn + r0, ldn, N + (int64_t)r0 * ldn + k0, ldn, N + (int64_t)k0 * ldn + r0, ldn,
+                                      rows, cols, nbe, -1.0, true, (tile / ntc) * LU_TR, (tile % ntc) * LU_TC, Ps, Qs);
         }
+        LU_MARK(4);
         cluster.sync();
+        LU_MARK(5);
     }
 
-    // ---- back substitution U X = Y (Y = columns M .. M+D-1 of N), CTA 0 ----
-    if (crank != 0) return;
-    double (*Ub)[LU_NB + 1] = Ps;                   // U block, 16 x 16
-    double (*Xb)[LU_TC] = Qs;                       // solved block rows, 16 x D   (D <= 64 < LU_TC)
-    const int nblk = (M + LU_NB - 1) / LU_NB;
-    for (int kb = nblk - 1; kb >= 0; --kb) {
-        const int k0 = kb * LU_NB, nbe = min(LU_NB, M - k0);
-        __syncthreads();
-        if (tid < LU_NB * LU_NB) {
-            const int i = tid / LU_NB, j = tid % LU_NB;
-            Ub[i][j] = (i < nbe && j < nbe && j >= i) ? N[(int64_t)(k0 + i) * ldn + k0 + j] : (i == j ? 1.0 : 0.0);
-        }
-        for (int e = tid; e < LU_NB * D; e += LU_THREADS) {
-            const int i = e / D, d = e % D;
-            Xb[i][d] = (i < nbe) ? N[(int64_t)(k0 + i) * ldn + M + d] : 0.0;
-        }
-        __syncthreads();
-        if (tid < D) {
-            for (int i = nbe - 1; i >= 0; --i) {
-                double s = Xb[i][tid];
-                for (int j = i + 1; j < nbe; ++j) s = fma(-Ub[i][j], Xb[j][tid], s);
-                Xb[i][tid] = s / Ub[i][i];
+    // ---- back substitution U X = Y (Y = columns M .. M+D-1 of N).  The right-hand sides are independent: CTA c takes the
+    // columns c, c + csize, ... (no exchange between CTAs).  Thread t keeps the entries of its rows t, t + 512, ... in
+    // registers.  Per block of 16 rows (bottom up): every thread whose row lies in or above the block loads its 16
+    // entries of U; the warp that owns the block's rows solves the 16 x 16 triangle with shuffles (v1 went through
+    // global memory and one thread per column: 585 us of 1.9 ms at M = 500); the solved block goes through shared
+    // memory to the rows above. ----
+    {
+        constexpr int RB = (LU_MAX_M + LU_THREADS - 1) / LU_THREADS;      // rows per thread, worst case
+        constexpr int NCMAX = 4;                                          // columns per pass
+        double (*Xs)[LU_NB][NCMAX] = reinterpret_cast<double (*)[LU_NB][NCMAX]>(&Qs[0][0]);   // [2][16][NCMAX]
+        const int nblk = (M + LU_NB - 1) / LU_NB;
+        for (int cbase = crank; cbase < D; cbase += csize * NCMAX) {
+            // this CTA's columns of the pass: cbase, cbase + csize, ... (up to NCMAX)
+            int ncol = 0;
+            int col[NCMAX];
+#pragma unroll
+            for (int c = 0; c < NCMAX; ++c) {
+                col[c] = cbase + c * csize;
+                if (col[c] < D) ncol = c + 1;
             }
+            double y[RB][NCMAX];
+#pragma unroll
+            for (int q = 0; q < RB; ++q)
+#pragma unroll
+                for (int c = 0; c < NCMAX; ++c) {
+                    const int r = tid + LU_THREADS * q;
+                    y[q][c] = (r < M && c < ncol) ? N[(int64_t)r * ldn + M + col[c]] : 0.0;
+                }
+            for (int kb = nblk - 1; kb >= 0; --kb) {
+                const int k0 = kb * LU_NB, nbe = min(LU_NB, M - k0), par = kb & 1;
+                const int qb = k0 / LU_THREADS, t0 = k0 % LU_THREADS;        // the block's rows: threads t0 .. t0 + nbe - 1, slot qb
+                if ((tid >> 5) == (t0 >> 5)) {
+                    // the warp that holds the block's rows: triangular solve with shuffles (lanes l0 .. l0 + nbe - 1)
+                    const int l0 = t0 & 31, li = lane - l0;
+                    const bool in_blk = li >= 0 && li < nbe;
+                    double useg[LU_NB], yb[NCMAX];
+#pragma unroll
+                    for (int jj = 0; jj < LU_NB; ++jj)
+                        useg[jj] = (in_blk && jj < nbe) ? N[(int64_t)(k0 + li) * ldn + k0 + jj] : 1.0;
+#pragma unroll
+                    for (int c = 0; c < NCMAX; ++c) {
+                        yb[c] = 0.0;
+#pragma unroll
+                        for (int q = 0; q < RB; ++q)
+                            if (q == qb) yb[c] = y[q][c];
+                    }
+                    // reciprocal of the own diagonal entry, once per row and off the 16-step chain (optimised BLAS trsm
+                    // kernels, OpenBLAS among them, keep the inverted diagonal too)
+                    double rdiag = 1.0;
+#pragma unroll
+                    for (int jj = 0; jj < LU_NB; ++jj)
+                        if (jj == li) rdiag = 1.0 / useg[jj];
+#pragma unroll
+                    for (int i = LU_NB - 1; i >= 0; --i) {
+                        if (i < nbe) {                          // uniform over the warp
+#pragma unroll
+                            for (int c = 0; c < NCMAX; ++c) {
+                                const double cand = yb[c] * rdiag;                    // meaningful on the lane of row k0 + i
+                                const double xi = __shfl_sync(0xffffffffu, cand, l0 + i);
+                                if (li == i) yb[c] = xi;
+                                else if (in_blk && li < i) yb[c] = fma(-useg[i], xi, yb[c]);
+                            }
+                        }
+                    }
+                    if (in_blk) {
+#pragma unroll
+                        for (int c = 0; c < NCMAX; ++c) {
+                            Xs[par][li][c] = yb[c];
+                            if (c < ncol) a.C[(int64_t)(k0 + li) * D + col[c]] = yb[c];
+                        }
+                    }
+                }
+                __syncthreads();
+                // rows above the block: y_r -= U[r][block] x_block
+#pragma unroll
+                for (int q = 0; q < RB; ++q) {
+                    const int r = tid + LU_THREADS * q;
+                    if (r < k0) {
+                        double useg[LU_NB];
+#pragma unroll
+                        for (int jj = 0; jj < LU_NB; ++jj) useg[jj] = (jj < nbe) ? N[(int64_t)r * ldn + k0 + jj] : 0.0;
+#pragma unroll
+                        for (int jj = 0; jj < LU_NB; ++jj)
+#pragma unroll
+                            for (int c = 0; c < NCMAX; ++c) y[q][c] = fma(-useg[jj], Xs[par][jj][c], y[q][c]);
+                    }
+                }
+            }
+            __syncthreads();
         }
-        __syncthreads();
-        for (int e = tid; e < nbe * D; e += LU_THREADS) a.C[(int64_t)(k0 + e / D) * D + e % D] = Xb[e / D][e % D];
-        for (int e = tid; e < k0 * D; e += LU_THREADS) {
-            const int i = e / D, d = e % D;
-            double s = N[(int64_t)i * ldn + M + d];
-            const double* urow = N + (int64_t)i * ldn + k0;
-#pragma unroll 4
-            for (int j = 0; j < nbe; ++j) s = fma(-urow[j], Xb[j][d], s);
-            N[(int64_t)i * ldn + M + d] = s;
-        }
+    }
+    __syncthreads();
+    LU_MARK(6);
+    if (tid == 0 && crank == 0) {
+        unsigned long long* dbg = reinterpret_cast<unsigned long long*>(a.piv + 32);
+        for (int i = 0; i < 8; ++i) dbg[i] = tacc[i];
     }
 }
 
 static inline int lu_ldn(int M, int D) { return (M + D + 1) & ~1; }
 
 size_t solve_normal_ws_bytes(int M, int D) {
-    return sizeof(double) * 2 * (size_t)M * lu_ldn(M, D) + 256;
+    return sizeof(double) * 2 * (size_t)M * lu_ldn(M, D) + 256;   // + pivots (16 ints) + 8 phase timers at byte 128
 }
 
-template <int R>
+template <int R, int PW>
 static int lu_launch_factor(const lu_args& a, cudaStream_t st) {
     static int cluster_size = 0;
     if (!cluster_size) {
-        DVF_CUDA(cudaFuncSetAttribute(k_lu_factor<R>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        DVF_CUDA(cudaFuncSetAttribute(k_lu_factor<R, PW>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         for (int cs : {16, 8, 4, 2, 1}) {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(cs); cfg.blockDim = dim3(LU_THREADS);
@@ -521,7 +626,7 @@ static int lu_launch_factor(const lu_args& a, cudaStream_t st) {
             at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
             cfg.attrs = at; cfg.numAttrs = 1;
             int n = 0;
-            if (cudaOccupancyMaxActiveClusters(&n, k_lu_factor<R>, &cfg) == cudaSuccess && n >= 1) { cluster_size = cs; break; }
+            if (cudaOccupancyMaxActiveClusters(&n, k_lu_factor<R, PW>, &cfg) == cudaSuccess && n >= 1) { cluster_size = cs; break; }
             cudaGetLastError();
         }
         if (!cluster_size) { set_error("k_lu_factor cannot be scheduled"); return DVF_ERR_CUDA; }
@@ -535,7 +640,7 @@ static int lu_launch_factor(const lu_args& a, cudaStream_t st) {
     at[0].val.clusterDim.x = cluster_size; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     ++g_launch_count;
-    DVF_CUDA(cudaLaunchKernelEx(&cfg, k_lu_factor<R>, a));
+    DVF_CUDA(cudaLaunchKernelEx(&cfg, k_lu_factor<R, PW>, a));
     return DVF_OK;
 }
 
@@ -556,11 +661,14 @@ int solve_normal_run(const double* G, int64_t ldg, const double* Kc, int M, int 
     if (nb > 4 * num_sms()) nb = 4 * num_sms();
     k_lu_prep<<<nb, 256, 0, st>>>(a);
     DVF_LAUNCH_CHECK();
-    k_lu_ata<<<((M + LU_TR - 1) / LU_TR) * ((W + LU_TC - 1) / LU_TC), LU_THREADS, 0, st>>>(a);
+    k_lu_ata<<<((M + LU_ATR - 1) / LU_ATR) * ((W + LU_ATC - 1) / LU_ATC), LU_THREADS, 0, st>>>(a);
     DVF_LAUNCH_CHECK();
-    if (M <= LU_THREADS) return lu_launch_factor<1>(a, st);
-    if (M <= 2 * LU_THREADS) return lu_launch_factor<2>(a, st);
-    return lu_launch_factor<4>(a, st);
+    // rows per thread x warps of the panel: fewer warps make the two barriers per column cheaper, more rows per thread
+    // cost registers (4 x 16 doubles spill)
+    if (M <= 256) return lu_launch_factor<1, 8>(a, st);
+    if (M <= 512) return lu_launch_factor<2, 8>(a, st);
+    if (M <= 1024) return lu_launch_factor<2, 16>(a, st);
+    return lu_launch_factor<4, 16>(a, st);
 }
 
 }  // namespace dvf
