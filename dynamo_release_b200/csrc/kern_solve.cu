@@ -333,6 +333,137 @@ __device__ __forceinline__ unsigned long long lu_now() {
         }                                                                \
     } while (0)
 
+// shared state of the panel factorisation
+struct lu_panel_smem {
+    double rowP[2][LU_NB];
+    double wval[2][LU_PWMAX], wsgn[2][LU_PWMAX];
+    int wpos[2][LU_PWMAX], wown[2][LU_PWMAX];
+    int s_piv[LU_NB];
+    double U12s[LU_NB][LU_NB + 1];
+};
+
+// Panel factorisation of the columns k0 .. k0 + 15 (rows k0 .. M - 1) by the first LU_PW warps of a CTA, R rows per thread
+// in registers, named barrier 1.  kprev >= 0: the trailing update of the PREVIOUS panel (columns kprev .. kprev + 15) has
+// not been applied to these columns yet and is done here while they are loaded (look-ahead: the other CTAs of the
+// cluster meanwhile update the rest of the trailing matrix).
+template <int R, int LU_PW>
+__device__ __forceinline__ void lu_panel(const lu_args& a, int k0, int kprev, lu_panel_smem& sh) {
+    constexpr int NOROW = 0x7fffffff;
+    const int M = a.M, ldn = a.ldn;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nbe = min(LU_NB, M - k0);
+    double* N = a.N;
+    constexpr int PT = LU_PW * 32;
+    double av[R][LU_NB];
+    int pos[R];
+    if (kprev >= 0) {       // look-ahead: U12 block of the previous panel above this panel's columns
+        for (int e = tid; e < LU_NB * LU_NB; e += PT) {
+            const int jj = e / LU_NB, c = e % LU_NB;
+            sh.U12s[jj][c] = (c < nbe) ? N[(int64_t)(kprev + jj) * ldn + k0 + c] : 0.0;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
+    }
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+        const int r = k0 + tid + PT * q;
+        pos[q] = r < M ? r : NOROW;
+#pragma unroll
+        for (int c = 0; c < LU_NB; ++c) av[q][c] = (r < M && c < nbe) ? N[(int64_t)r * ldn + k0 + c] : 0.0;
+        if (kprev >= 0 && r < M) {
+            // the previous panel's trailing update of these 16 columns, in registers: N22 -= L21 U12 (same arithmetic as
+            // lu_tile: the sum first, then one fma into the entry)
+            double lrow[LU_NB];
+#pragma unroll
+            for (int jj = 0; jj < LU_NB; ++jj) lrow[jj] = N[(int64_t)r * ldn + kprev + jj];
+#pragma unroll
+            for (int c = 0; c < LU_NB; ++c) {
+                double sacc = 0.0;
+#pragma unroll
+                for (int jj = 0; jj < LU_NB; ++jj) sacc = fma(lrow[jj], sh.U12s[jj][c], sacc);
+                av[q][c] = fma(-1.0, sacc, av[q][c]);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < LU_NB; ++j) {
+        if (j < nbe) {                     // uniform over the panel warps
+            const int par = j & 1;
+            // arg-max of |column j| over the rows not yet eliminated: the magnitude first (5 shuffles), then the
+            // smallest logical row among the lanes that hold it (one ballot unless magnitudes tie)
+            double bv = -1.0, bs = 0.0;
+            int bp = NOROW, bo = 0;
+#pragma unroll
+            for (int q = 0; q < R; ++q) {
+                const double v = fabs(av[q][j]);
+                if (pos[q] != NOROW && pos[q] >= k0 + j && (v > bv || (v == bv && pos[q] < bp))) {
+                    bv = v; bs = av[q][j]; bp = pos[q]; bo = tid * R + q;
+                }
+            }
+            double wv = bv;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) wv = fmax(wv, __shfl_xor_sync(0xffffffffu, wv, o));
+            const unsigned eq = __ballot_sync(0xffffffffu, bv == wv && bp != NOROW);
+            if (__popc(eq) > 1) {          // tie in magnitude: LAPACK's idamax takes the first row
+                int mp = (bv == wv) ? bp : NOROW;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) mp = min(mp, __shfl_xor_sync(0xffffffffu, mp, o));
+                const unsigned eq2 = __ballot_sync(0xffffffffu, bv == wv && bp == mp);
+                if (lane == __ffs(eq2) - 1) { sh.wval[par][warp] = bv; sh.wsgn[par][warp] = bs; sh.wpos[par][warp] = bp; sh.wown[par][warp] = bo; }
+            } else if (eq == 0) {          // no candidate in this warp (all its rows are eliminated / NaN)
+                if (lane == 0) { sh.wval[par][warp] = -1.0; sh.wsgn[par][warp] = 0.0; sh.wpos[par][warp] = NOROW; sh.wown[par][warp] = 0; }
+            } else if (lane == __ffs(eq) - 1) {
+                sh.wval[par][warp] = bv; sh.wsgn[par][warp] = bs; sh.wpos[par][warp] = bp; sh.wown[par][warp] = bo;
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
+            bv = -1.0; bs = 0.0; bp = NOROW; bo = 0;
+#pragma unroll
+            for (int w = 0; w < LU_PW; ++w) {   // broadcast reads; every thread scans the LU_PW candidates
+                const double v = sh.wval[par][w];
+                const int p2 = sh.wpos[par][w];
+                if (v > bv || (v == bv && p2 < bp)) { bv = v; bs = sh.wsgn[par][w]; bp = p2; bo = sh.wown[par][w]; }
+            }
+            // LAPACK getf2 scales the column by the reciprocal of the pivot (|pivot| >= sfmin); the division
+            // runs while the pivot row travels through shared memory
+            const double rpv = 1.0 / bs;
+            if (tid == 0) {
+                sh.s_piv[j] = bp;
+                if (!(bv > 0.0)) atomicCAS(a.info, 0, k0 + j + 1);      // exactly singular (or NaN)
+            }
+#pragma unroll
+            for (int q = 0; q < R; ++q) {
+                if (tid * R + q == bo) {             // this thread holds the pivot row: it becomes row k0 + j
+#pragma unroll
+                    for (int c = 0; c < LU_NB; ++c) sh.rowP[par][c] = av[q][c];
+                    pos[q] = k0 + j;
+                } else if (pos[q] == k0 + j) {
+                    pos[q] = bp;                     // the row that sat at k0 + j goes where the pivot row was
+                }
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
+#pragma unroll
+            for (int q = 0; q < R; ++q) {
+                if (pos[q] != NOROW && pos[q] > k0 + j) {
+                    const double l = av[q][j] * rpv;
+                    av[q][j] = l;
+#pragma unroll
+                    for (int c = 0; c < LU_NB; ++c)
+                        if (c > j) av[q][c] = fma(-l, sh.rowP[par][c], av[q][c]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < R; ++q) {
+        if (pos[q] != NOROW) {
+#pragma unroll
+            for (int c = 0; c < LU_NB; ++c)
+                if (c < nbe) N[(int64_t)pos[q] * ldn + k0 + c] = av[q][c];
+        }
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
+    if (tid < nbe) a.piv[(k0 / LU_NB & 1) * LU_NB + tid] = sh.s_piv[tid];
+}
+
 template <int R, int LU_PW>
 __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
     cg::cluster_group cluster = cg::this_cluster();
@@ -340,113 +471,19 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
     unsigned long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tlast = lu_now();
     __shared__ double Ps[LU_TR][LU_NB + 1];
     __shared__ double Qs[LU_NB][LU_TC];
-    __shared__ double rowP[2][LU_NB];
-    __shared__ double wval[2][LU_PWMAX], wsgn[2][LU_PWMAX];
-    __shared__ int wpos[2][LU_PWMAX], wown[2][LU_PWMAX];
-    __shared__ int s_piv[LU_NB];
+    __shared__ lu_panel_smem sh;
     __shared__ int s_tp[2 * LU_NB], s_ts[2 * LU_NB], s_np;
     const int M = a.M, D = a.D, W = a.M + a.D, ldn = a.ldn;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int crank = (int)cluster.block_rank(), csize = (int)cluster.num_blocks();
     double* N = a.N;
-    constexpr int NOROW = 0x7fffffff;
-
+    // panel 0; every later panel is factored by CTA 0 during the trailing update of the panel before it (look-ahead)
+    if (crank == 0 && warp < LU_PW) lu_panel<R, LU_PW>(a, 0, -1, sh);
+    LU_MARK(0);
+    cluster.sync();
+    LU_MARK(1);
     for (int k0 = 0; k0 < M; k0 += LU_NB) {
         const int nbe = min(LU_NB, M - k0);
-        // ---- (a) panel factorisation: the first LU_PW warps of CTA 0, R rows per thread, named barrier 1 ----
-        if (crank == 0 && warp < LU_PW) {
-            constexpr int PT = LU_PW * 32;
-            double av[R][LU_NB];
-            int pos[R];
-#pragma unroll
-            for (int q = 0; q < R; ++q) {
-                const int r = k0 + tid + PT * q;
-                pos[q] = r < M ? r : NOROW;
-#pragma unroll
-                for (int c = 0; c < LU_NB; ++c) av[q][c] = (r < M && c < nbe) ? N[(int64_t)r * ldn + k0 + c] : 0.0;
-            }
-#pragma unroll
-            for (int j = 0; j < LU_NB; ++j) {
-                if (j < nbe) {                     // uniform over the panel warps
-                    const int par = j & 1;
-                    // arg-max of |column j| over the rows not yet eliminated: the magnitude first (5 shuffles), then the
-                    // smallest logical row among the lanes that hold it (one ballot unless magnitudes tie)
-                    double bv = -1.0, bs = 0.0;
-                    int bp = NOROW, bo = 0;
-#pragma unroll
-                    for (int q = 0; q < R; ++q) {
-                        const double v = fabs(av[q][j]);
-                        if (pos[q] != NOROW && pos[q] >= k0 + j && (v > bv || (v == bv && pos[q] < bp))) {
-                            bv = v; bs = av[q][j]; bp = pos[q]; bo = tid * R + q;
-                        }
-                    }
-                    double wv = bv;
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) wv = fmax(wv, __shfl_xor_sync(0xffffffffu, wv, o));
-                    const unsigned eq = __ballot_sync(0xffffffffu, bv == wv && bp != NOROW);
-                    if (__popc(eq) > 1) {          // tie in magnitude: LAPACK's idamax takes the first row
-                        int mp = (bv == wv) ? bp : NOROW;
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) mp = min(mp, __shfl_xor_sync(0xffffffffu, mp, o));
-                        const unsigned eq2 = __ballot_sync(0xffffffffu, bv == wv && bp == mp);
-                        if (lane == __ffs(eq2) - 1) { wval[par][warp] = bv; wsgn[par][warp] = bs; wpos[par][warp] = bp; wown[par][warp] = bo; }
-                    } else if (eq == 0) {          // no candidate in this warp (all its rows are eliminated / NaN)
-                        if (lane == 0) { wval[par][warp] = -1.0; wsgn[par][warp] = 0.0; wpos[par][warp] = NOROW; wown[par][warp] = 0; }
-                    } else if (lane == __ffs(eq) - 1) {
-                        wval[par][warp] = bv; wsgn[par][warp] = bs; wpos[par][warp] = bp; wown[par][warp] = bo;
-                    }
-                    asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
-                    bv = -1.0; bs = 0.0; bp = NOROW; bo = 0;
-#pragma unroll
-                    for (int w = 0; w < LU_PW; ++w) {   // broadcast reads; every thread scans the LU_PW candidates
-                        const double v = wval[par][w];
-                        const int p2 = wpos[par][w];
-                        if (v > bv || (v == bv && p2 < bp)) { bv = v; bs = wsgn[par][w]; bp = p2; bo = wown[par][w]; }
-                    }
-                    // LAPACK getf2 scales the column by the reciprocal of the pivot (|pivot| >= sfmin); the division
-                    // runs while the pivot row travels through shared memory
-                    const double rpv = 1.0 / bs;
-                    if (tid == 0) {
-                        s_piv[j] = bp;
-                        if (!(bv > 0.0)) atomicCAS(a.info, 0, k0 + j + 1);      // exactly singular (or NaN)
-                    }
-#pragma unroll
-                    for (int q = 0; q < R; ++q) {
-                        if (tid * R + q == bo) {             // this thread holds the pivot row: it becomes row k0 + j
-#pragma unroll
-                            for (int c = 0; c < LU_NB; ++c) rowP[par][c] = av[q][c];
-                            pos[q] = k0 + j;
-                        } else if (pos[q] == k0 + j) {
-                            pos[q] = bp;                     // the row that sat at k0 + j goes where the pivot row was
-                        }
-                    }
-                    asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
-#pragma unroll
-                    for (int q = 0; q < R; ++q) {
-                        if (pos[q] != NOROW && pos[q] > k0 + j) {
-                            const double l = av[q][j] * rpv;
-                            av[q][j] = l;
-#pragma unroll
-                            for (int c = 0; c < LU_NB; ++c)
-                                if (c > j) av[q][c] = fma(-l, rowP[par][c], av[q][c]);
-                        }
-                    }
-                }
-            }
-#pragma unroll
-            for (int q = 0; q < R; ++q) {
-                if (pos[q] != NOROW) {
-#pragma unroll
-                    for (int c = 0; c < LU_NB; ++c)
-                        if (c < nbe) N[(int64_t)pos[q] * ldn + k0 + c] = av[q][c];
-                }
-            }
-            asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
-            if (tid < nbe) a.piv[tid] = s_piv[tid];
-        }
-        LU_MARK(0);
-        cluster.sync();
-        LU_MARK(1);
         // ---- (b) the panel's row swaps applied to the columns right of it (incl. the right-hand sides), fused with
         //      U12 = L11^-1 N12.  The 16 swaps are composed first: position tp[i] receives the old row ts[i]. ----
         {
@@ -458,7 +495,7 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
             if (warp == 0) {       // lane i holds touched position tp and the old row ts that ends up there
                 int np = nbe;
                 int tp = lane < nbe ? k0 + lane : -1, ts = tp;
-                const int mypiv = lane < nbe ? a.piv[lane] : 0;
+                const int mypiv = lane < nbe ? a.piv[(k0 / LU_NB & 1) * LU_NB + lane] : 0;
                 for (int j = 0; j < nbe; ++j) {
                     const int p = __shfl_sync(0xffffffffu, mypiv, j);
                     const unsigned hit = __ballot_sync(0xffffffffu, lane < np && tp == p);
@@ -494,14 +531,21 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
         LU_MARK(2);
         cluster.sync();
         LU_MARK(3);
-        // ---- (c) trailing update N22 -= L21 U12 ----
+        // ---- (c) trailing update N22 -= L21 U12.  CTA 0 applies it to the NEXT panel's 16 columns only and factors that
+        //      panel right away; the other CTAs take the rest of the trailing matrix meanwhile ----
         const int r0 = k0 + nbe;
         if (r0 < M) {
-            const int rows = M - r0, cols = W - r0;
-            const int ntr = (rows + LU_TR - 1) / LU_TR, ntc = (cols + LU_TC - 1) / LU_TC;
-            for (int tile = crank; tile < ntr * ntc; tile += csize)
-                lu_tile<LU_TR, LU_TC>(N + (int64_t)r0 * ldn + r0, ldn, N + (int64_t)r0 * ldn + k0, ldn, N + (int64_t)k0 * ldn + r0, ldn,
-                                      rows, cols, nbe, -1.0, true, (tile / ntc) * LU_TR, (tile % ntc) * LU_TC, Ps, Qs);
+            const int nb2 = min(LU_NB, M - r0), c0 = r0 + nb2;
+            if (crank == 0 && warp < LU_PW) lu_panel<R, LU_PW>(a, r0, k0, sh);
+            if (csize == 1 || crank != 0) {
+                const int workers = csize == 1 ? 1 : csize - 1, me = csize == 1 ? 0 : crank - 1;
+                const int rows = M - r0, cols = W - c0;
+                const int ntr = (rows + LU_TR - 1) / LU_TR, ntc = (cols + LU_TC - 1) / LU_TC;
+                for (int tile = me; tile < ntr * ntc; tile += workers)
+                    lu_tile<LU_TR, LU_TC>(N + (int64_t)r0 * ldn + c0, ldn, N + (int64_t)r0 * ldn + k0, ldn,
+                                          N + (int64_t)k0 * ldn + c0, ldn, rows, cols, nbe, -1.0, true,
+                                          (tile / ntc) * LU_TR, (tile % ntc) * LU_TC, Ps, Qs);
+            }
         }
         LU_MARK(4);
         cluster.sync();
@@ -665,6 +709,9 @@ int solve_normal_run(const double* G, int64_t ldg, const double* Kc, int M, int 
     DVF_LAUNCH_CHECK();
     // rows per thread x warps of the panel: fewer warps make the two barriers per column cheaper, more rows per thread
     // cost registers (4 x 16 doubles spill)
+    static const char* pw = getenv("DVF_LU_PW");           // developer knob (tools/solve_tune.py)
+    if (pw && atoi(pw) == 16 && M <= 512) return lu_launch_factor<1, 16>(a, st);
+    if (pw && atoi(pw) == 4 && M <= 512) return lu_launch_factor<4, 4>(a, st);
     if (M <= 256) return lu_launch_factor<1, 8>(a, st);
     if (M <= 512) return lu_launch_factor<2, 8>(a, st);
     if (M <= 1024) return lu_launch_factor<2, 16>(a, st);
