@@ -12,7 +12,7 @@ else
   B="python bench.py"
 fi
 $B --gpus $N --steps 3 --warmup 3 > gpurun_out/${TAG}_weak_c3_n$N.json 2> gpurun_out/${TAG}_weak_c3_n$N.err; echo "weak rc=$?"
-$B --gpus $N --steps 3 --warmup 3 --scaling strong --no-cpu-baseline > gpurun_out/${TAG}_strong_c3_n$N.json 2> gpurun_out/${TAG}_strong_c3_n$N.err; echo "strong rc=$?"
+$B --gpus $N --steps 2 --warmup 2 --scaling strong --no-cpu-baseline > gpurun_out/${TAG}_strong_c3_n$N.json 2> gpurun_out/${TAG}_strong_c3_n$N.err; echo "strong rc=$?"
 $B --gpus $N --steps 2 --warmup 2 --workload c5 --no-cpu-baseline --no-e2e > gpurun_out/${TAG}_strong_c5_n$N.json 2> gpurun_out/${TAG}_strong_c5_n$N.err; echo "c5 rc=$?"
 for f in weak_c3 strong_c3 strong_c5; do python - <<PY
 import json
