@@ -12,6 +12,8 @@ from .svc import SvcVectorField, vecfld_from_adata  # noqa: F401
 from .integrate import (  # noqa: F401
     DenseSolution, ScaledRkhsField, _fate, dense_eval_many, integrate_vf_ivp, solve_ivp_batch,
 )
+from .lap import action, action_grad, least_action_path  # noqa: F401
+from .rank import rank_jacobian_genes  # noqa: F401
 from .vf import (  # noqa: F401
     Hessian_rkhs_gaussian,
     Laplacian,

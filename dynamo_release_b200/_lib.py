@@ -46,6 +46,7 @@ SIGNATURES = {
     "dvf_jacobian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
     "dvf_jacobian_workspace_bytes": (_i, [_i64, _i, _i, C.POINTER(_sz)]),
     "dvf_jacobian_ws": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p, _sz, _p]),
+    "dvf_lap_terms": (_i, [_p, _p, _i64, _i, _p, _i, _d, _p, _p, _p, _p]),
     "dvf_div_acc_curv": (_i, [_p, _i64, _i, _p, _i, _d, _p, _i, _p, _p, _p, _p, _p, _p, _p]),
     "dvf_gene_transform": (_i, [_p, _i64, _i, _p, _i, _p, _i, _i, _p, _i, _p, _p, _p]),
     "dvf_gene_gemm_workspace_bytes": (_i, [_i64, _i, _i, _i, _i, _i, C.POINTER(_sz)]),
@@ -57,6 +58,8 @@ SIGNATURES = {
     "dvf_cell_angles": (_i, [_p, _p, _i64, _i, _p, _p]),
     "dvf_row_norms": (_i, [_p, _i64, _i, _p, _p]),
     "dvf_knn_dists": (_i, [_p, _i, _i, _i, _p, _p]),
+    "dvf_f32_row_means_pairwise": (_i, [_p, _i64, _i64, _p, _i, _p, _p]),
+    "dvf_f32_group_means_seq": (_i, [_p, _i64, _i64, _p, _i, _p, _p, _p]),
     "dvf_hessian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
     "dvf_laplacian": (_i, [_p, _i64, _i, _p, _i, _d, _p, _p, _p]),
     "dvf_ivp_workspace_bytes": (_i, [_i, _i, C.POINTER(_sz)]),

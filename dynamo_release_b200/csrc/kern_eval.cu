@@ -282,6 +282,76 @@ __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64
     }
 }
 
+// Least-action-path terms (reference vectorfield/least_action_path.py:7-57): per path segment with centre x and
+// finite-difference velocity vp,   dv = vp - f(x)   and   z = dv J(x)   (the row-vector / Jacobian product action_grad needs),
+// without materialising J:  z_j = -2 beta sum_m k_m (dv . C_m) (x_j - c_mj).  Same skeleton as k_dac (one thread per point,
+// two passes over the control points, the second one with the complete dv).  D <= 32.
+template <int DP>
+__global__ void __launch_bounds__(128) k_lap_terms(const double* __restrict__ x, const double* __restrict__ vp, int64_t n,
+                                                   int D, const double* __restrict__ Xc, int M, double beta,
+                                                   const double* __restrict__ C, double* __restrict__ dv_out,
+                                                   double* __restrict__ z_out) {
+    __shared__ double cs[ev_chunk<DP>::MC * DP];
+    __shared__ double Cs[ev_chunk<DP>::MC * DP];
+    const int64_t cell = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = cell < n;
+    double xr[DP], wr[DP];
+#pragma unroll
+    for (int d = 0; d < DP; ++d) { xr[d] = (live && d < D) ? x[cell * D + d] : 0.0; wr[d] = 0.0; }
+    for (int m0 = 0; m0 < M; m0 += ev_chunk<DP>::MC) {
+        const int mc = min(ev_chunk<DP>::MC, M - m0);
+        __syncthreads();
+        load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
+        __syncthreads();
+        for (int m = 0; m < mc; ++m) {
+            double d2a = 0.0, d2b = 0.0;
+#pragma unroll
+            for (int d = 0; d < DP; d += 2) {
+                double ta = xr[d] - cs[m * DP + d], tb = xr[d + 1] - cs[m * DP + d + 1];
+                d2a = fma(ta, ta, d2a);
+                d2b = fma(tb, tb, d2b);
+            }
+            const double k = exp(-beta * (d2a + d2b));
+#pragma unroll
+            for (int d = 0; d < DP; ++d) wr[d] = fma(k, Cs[m * DP + d], wr[d]);
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < DP; ++d) wr[d] = (live && d < D) ? vp[cell * D + d] - wr[d] : 0.0;     // dv = vp - f(x)
+    double zr[DP];
+#pragma unroll
+    for (int d = 0; d < DP; ++d) zr[d] = 0.0;
+    if (z_out) {
+        for (int m0 = 0; m0 < M; m0 += ev_chunk<DP>::MC) {
+            const int mc = min(ev_chunk<DP>::MC, M - m0);
+            __syncthreads();
+            load_chunk<DP>(cs, Cs, Xc, C, D, m0, mc);
+            __syncthreads();
+            for (int m = 0; m < mc; ++m) {
+                double d2a = 0.0, d2b = 0.0, sa = 0.0, sb = 0.0;
+#pragma unroll
+                for (int d = 0; d < DP; d += 2) {
+                    double ta = xr[d] - cs[m * DP + d], tb = xr[d + 1] - cs[m * DP + d + 1];
+                    d2a = fma(ta, ta, d2a);
+                    d2b = fma(tb, tb, d2b);
+                    sa = fma(wr[d], Cs[m * DP + d], sa);
+                    sb = fma(wr[d + 1], Cs[m * DP + d + 1], sb);
+                }
+                const double ks = exp(-beta * (d2a + d2b)) * (sa + sb);
+#pragma unroll
+                for (int d = 0; d < DP; ++d) zr[d] = fma(ks, xr[d] - cs[m * DP + d], zr[d]);
+            }
+        }
+    }
+    if (!live) return;
+#pragma unroll
+    for (int d = 0; d < DP; ++d)
+        if (d < D) {
+            if (dv_out) dv_out[cell * D + d] = wr[d];
+            if (z_out) z_out[cell * D + d] = -2.0 * beta * zr[d];
+        }
+}
+
 // K7 for D > 32: x, v and a of one cell no longer fit the register file of one thread (D = 50: 696 bytes of spills in
 // the kernel above), so TWO adjacent lanes share a cell, each holding HD = DP / 2 of its dimensions; the partial
 // distances and dot products are completed with one shuffle each.  Same arithmetic per dimension as k_dac; the two
@@ -510,6 +580,20 @@ extern "C" int dvf_div_acc_curv(const double* x, int64_t n, int D, const double*
         constexpr int DP = decltype(dp)::value;
         k_dac<DP><<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(x, n, D, Xc, M, beta, C, formula, v, div,
                                                                               acc, acc_norm, curv, curv_norm);
+        DVF_LAUNCH_CHECK();
+        return DVF_OK;
+    });
+}
+
+extern "C" int dvf_lap_terms(const double* x, const double* vp, int64_t n, int D, const double* Xc, int M, double beta,
+                             const double* C, double* dv, double* z, void* stream) {
+    if (int rc = check_field_args(x, n, D, Xc, M)) return rc;
+    DVF_ARG(C && vp, "NULL pointer");
+    DVF_ARG(D <= 32, "dvf_lap_terms serves D <= 32 (D = %d)", D);
+    if (n == 0) return DVF_OK;
+    return dispatch_dp(D, [&](auto dp) {
+        constexpr int DP = decltype(dp)::value;
+        k_lap_terms<DP><<<(unsigned)((n + 127) / 128), 128, 0, (cudaStream_t)stream>>>(x, vp, n, D, Xc, M, beta, C, dv, z);
         DVF_LAUNCH_CHECK();
         return DVF_OK;
     });

@@ -402,3 +402,129 @@ extern "C" int dvf_knn_dists(const double* Xc, int M, int D, int kk, double* out
     DVF_LAUNCH_CHECK();
     return DVF_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Cell reductions of the MATERIALISED gene-space Jacobian (Ge, Gr, n) float32 in NumPy's own float32 orders, so that
+// the means rank_jacobian_genes sorts (reference rank_vf.py:483-508) come out bit for bit -- north_star: "top-k
+// regulator rankings must match exactly".
+//   dvf_f32_row_means_pairwise : np.mean(J, axis=2) of a C-contiguous float32 array = (0 + pairwise_sum(row)) / n in
+//       float32.  pairwise_sum (numpy/_core/src/umath/loops_utils.h): n < 8 straight loop; n <= 128 eight interleaved
+//       accumulators combined ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)) plus a sequential tail; else halves split at
+//       n/2 rounded down to a multiple of 8, recursively.  The tree only depends on n: the host lists its leaves and,
+//       per leaf, how many pending additions close after it; a warp sums 32 leaves at a time (one per lane) and lane 0
+//       replays the additions on a small stack.
+//   dvf_f32_group_means_seq : average_jacobian_by_group (vectorfield/utils.py:557-582): per group a running float32
+//       sum over the cells in order, divided by the count.  One thread per (effector, regulator) row walks the cells
+//       sequentially; rows go through shared memory in 128 x 32 tiles so that the global loads are coalesced.
+// ---------------------------------------------------------------------------------------------------------
+namespace dvf {
+
+__device__ __forceinline__ float f32_leaf_sum(const float* __restrict__ a, int n) {
+    if (n < 8) {
+        float res = 0.0f;
+        for (int i = 0; i < n; ++i) res = __fadd_rn(res, a[i]);
+        return res;
+    }
+    float r[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r[j] = a[j];
+    int i = 8;
+    for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = __fadd_rn(r[j], a[i + j]);
+    }
+    float res = __fadd_rn(__fadd_rn(__fadd_rn(r[0], r[1]), __fadd_rn(r[2], r[3])),
+                          __fadd_rn(__fadd_rn(r[4], r[5]), __fadd_rn(r[6], r[7])));
+    for (; i < n; ++i) res = __fadd_rn(res, a[i]);
+    return res;
+}
+
+// leaves: (lo, len, adds_after) triples; one warp per row
+__global__ void __launch_bounds__(256) k_f32_row_means_pairwise(const float* __restrict__ J, int64_t R, int64_t n,
+                                                                const int* __restrict__ leaves, int n_leaves,
+                                                                float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= R) return;
+    const float* a = J + row * n;
+    float stack[40];
+    int sp = 0;
+    for (int l0 = 0; l0 < n_leaves; l0 += 32) {
+        const int k = l0 + lane;
+        float s = 0.0f;
+        int adds = 0;
+        if (k < n_leaves) {
+            s = f32_leaf_sum(a + leaves[3 * k], leaves[3 * k + 1]);
+            adds = leaves[3 * k + 2];
+        }
+        const int cnt = min(32, n_leaves - l0);
+        for (int q = 0; q < cnt; ++q) {
+            const float v = __shfl_sync(0xffffffffu, s, q);
+            const int na = __shfl_sync(0xffffffffu, adds, q);
+            if (lane == 0) {
+                stack[sp++] = v;
+                for (int t = 0; t < na; ++t) { const float b = stack[--sp], c = stack[--sp]; stack[sp++] = __fadd_rn(c, b); }
+            }
+        }
+    }
+    if (lane == 0) out[row] = __fdiv_rn(__fadd_rn(0.0f, stack[0]), (float)n);
+}
+
+constexpr int GS_ROWS = 128, GS_CELLS = 32;
+__global__ void __launch_bounds__(GS_ROWS) k_f32_group_means_seq(const float* __restrict__ J, int64_t R, int64_t n,
+                                                                 const int* __restrict__ label, int G,
+                                                                 const float* __restrict__ count, float* __restrict__ out) {
+    extern __shared__ float gs_smem[];
+    float (*tile)[GS_CELLS + 1] = reinterpret_cast<float (*)[GS_CELLS + 1]>(gs_smem);       // [GS_ROWS][33]
+    float* acc = gs_smem + GS_ROWS * (GS_CELLS + 1);                                         // [G][GS_ROWS]
+    int* lab = reinterpret_cast<int*>(acc + (size_t)G * GS_ROWS);                            // [GS_CELLS]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t row0 = (int64_t)blockIdx.x * GS_ROWS;
+    for (int g = 0; g < G; ++g) acc[g * GS_ROWS + tid] = 0.0f;
+    for (int64_t c0 = 0; c0 < n; c0 += GS_CELLS) {
+        __syncthreads();
+        // coalesced: a warp loads 32 consecutive cells of one row per request
+        for (int r = warp; r < GS_ROWS; r += GS_ROWS / 32) {
+            const int64_t row = row0 + r, c = c0 + lane;
+            tile[r][lane] = (row < R && c < n) ? J[row * n + c] : 0.0f;
+        }
+        if (tid < GS_CELLS) lab[tid] = (c0 + tid < n) ? label[c0 + tid] : -1;
+        __syncthreads();
+#pragma unroll 8
+        for (int c = 0; c < GS_CELLS; ++c) {
+            const int g = lab[c];
+            if (g >= 0) acc[g * GS_ROWS + tid] = __fadd_rn(acc[g * GS_ROWS + tid], tile[tid][c]);
+        }
+    }
+    if (row0 + tid < R)
+        for (int g = 0; g < G; ++g) out[(int64_t)g * R + row0 + tid] = __fdiv_rn(acc[g * GS_ROWS + tid], count[g]);
+}
+
+}  // namespace dvf
+
+extern "C" int dvf_f32_row_means_pairwise(const float* J, int64_t R, int64_t n, const int* leaves, int n_leaves,
+                                          float* out, void* stream) {
+    DVF_ARG(R >= 0 && n >= 1 && n_leaves >= 1, "bad argument");
+    if (R == 0) return DVF_OK;
+    DVF_ARG(J && leaves && out, "null pointer");
+    const int64_t blocks = (R + 7) / 8;
+    DVF_ARG(blocks <= 0x7fffffff, "too many rows for one launch");
+    dvf::k_f32_row_means_pairwise<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(J, R, n, leaves, n_leaves, out);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}
+
+extern "C" int dvf_f32_group_means_seq(const float* J, int64_t R, int64_t n, const int* label, int G, const float* count,
+                                       float* out, void* stream) {
+    DVF_ARG(R >= 0 && n >= 1 && G >= 1, "bad argument");
+    if (R == 0) return DVF_OK;
+    DVF_ARG(J && label && count && out, "null pointer");
+    const size_t smem = sizeof(float) * ((size_t)dvf::GS_ROWS * (dvf::GS_CELLS + 1) + (size_t)G * dvf::GS_ROWS) + sizeof(int) * dvf::GS_CELLS;
+    DVF_ARG(smem <= 200 * 1024, "too many groups for dvf_f32_group_means_seq (%d)", G);
+    if (smem > 48 * 1024) DVF_CUDA(cudaFuncSetAttribute(dvf::k_f32_group_means_seq, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t blocks = (R + dvf::GS_ROWS - 1) / dvf::GS_ROWS;
+    DVF_ARG(blocks <= 0x7fffffff, "too many rows for one launch");
+    dvf::k_f32_group_means_seq<<<(unsigned)blocks, dvf::GS_ROWS, smem, (cudaStream_t)stream>>>(J, R, n, label, G, count, out);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}

@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import importlib
 
-from . import integrate, svc, vf
+from . import integrate, lap, rank, svc, vf
 from .sparsevfc import SparseVFC
 
 _NAMES = {
@@ -32,12 +32,21 @@ _NAMES = {
     "vecfld_from_adata": svc.vecfld_from_adata,
     "integrate_vf_ivp": integrate.integrate_vf_ivp,
     "_fate": integrate._fate,
+    "rank_jacobian_genes": rank.rank_jacobian_genes,
+    "action": lap.action,
+    "action_aux": lap.action_aux,
+    "action_grad": lap.action_grad,
+    "action_grad_aux": lap.action_grad_aux,
+    "least_action_path": lap.least_action_path,
     "SparseVFC": SparseVFC,
     "SvcVectorField": svc.SvcVectorField,
 }
 _MODULES = ("dynamo.vectorfield.utils", "dynamo.vectorfield.scVectorField", "dynamo.vectorfield.vector_calculus",
             "dynamo.vectorfield.VectorField", "dynamo.vectorfield.rank_vf", "dynamo.vectorfield", "dynamo.vf", "dynamo.prediction.utils",
-            "dynamo.prediction.fate")
+            "dynamo.prediction.fate", "dynamo.vectorfield.least_action_path", "dynamo.prediction.least_action_path")
+# prediction/least_action_path.py has its OWN least_action_path (time-step optimisation around lap_T, :423-480) on top
+# of the same action / action_grad: only the four functional names are rebound there, its driver stays
+_SKIP = {("dynamo.prediction.least_action_path", "least_action_path")}
 _saved = {}
 _combined = {}
 
@@ -73,6 +82,8 @@ def install(modules=_MODULES):
         except Exception:
             continue
         for name, fn in names.items():
+            if (modname, name) in _SKIP:
+                continue
             if hasattr(mod, name) and getattr(mod, name) is not fn:
                 _saved[(modname, name)] = getattr(mod, name)
                 setattr(mod, name, fn)

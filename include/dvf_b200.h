@@ -57,6 +57,12 @@ int dvf_jacobian_workspace_bytes(int64_t n, int D, int M, size_t* out);
 int dvf_jacobian_ws(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
                     double* J, void* ws, size_t ws_bytes, void* stream);
 
+/* Least-action-path terms (vectorfield/least_action_path.py:7-57, `action` / `action_grad`): for n path segments with
+ * centres x (n x D) and finite-difference velocities vp (n x D):  dv = vp - f(x)  and  z = dv J(x)  (row vector times
+ * Jacobian, the loop of :50-52) without materialising J.  Either output may be NULL.  D <= 32. */
+int dvf_lap_terms(const double* x, const double* vp, int64_t n, int D, const double* Xc, int M, double beta,
+                  const double* C, double* dv, double* z, void* stream);
+
 /* K7: fused divergence / acceleration / curvature without materialising J.  Any output may be NULL.
  *   v (n x D) = f(x);  div (n) = tr J;  acc (n x D) = J v;  acc_norm (n) = |acc|;
  *   formula 2: curv (n x D) = (a (v.v) - v (v.a)) / |v|^4, curv_norm = |curv|;
@@ -110,6 +116,17 @@ int dvf_vector_transform(const double* V, int64_t n, int D, const double* Q, int
 int dvf_jacobian_det(const double* J, int64_t n, int D, double* det, void* stream);
 int dvf_cell_angles(const double* U, const double* V, int64_t n, int D, double* out, void* stream);
 int dvf_row_norms(const double* V, int64_t n, int D, double* out, void* stream);
+/* Cell reductions of the materialised gene-space Jacobian J (R = Ge*Gr rows of n float32 cells, the reference's
+ * `jacobian_gene` layout) in NumPy's own float32 summation orders, so that the means rank_jacobian_genes sorts
+ * (vectorfield/rank_vf.py:483-508) are bit-identical:
+ *   dvf_f32_row_means_pairwise: out[r] = np.mean(J[r]) -- pairwise float32 sum (leaves: n_leaves triples
+ *     {first cell, length, additions that close after this leaf} of NumPy's pairwise tree for n, built by the host);
+ *   dvf_f32_group_means_seq: out[g][r] = running float32 sum of J[r][c] over the cells with label[c] == g, in cell
+ *     order, divided by count[g] (vectorfield/utils.py:557-582, average_jacobian_by_group); label < 0 skips a cell. */
+int dvf_f32_row_means_pairwise(const float* J, int64_t R, int64_t n, const int* leaves, int n_leaves,
+                               float* out, void* stream);
+int dvf_f32_group_means_seq(const float* J, int64_t R, int64_t n, const int* label, int G, const float* count,
+                            float* out, void* stream);
 /* bandwidth_selector's neighbour search (scVectorField.py:121-135 -> tools/connectivity.py:565-577, exact kNN): out
  * (M x kk, row-major) = Euclidean distances from control point i to its kk nearest control points, itself included,
  * ascending.  Squared distances are summed dimension by dimension with separate multiply / add (sklearn's order). */

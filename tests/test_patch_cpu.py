@@ -34,7 +34,8 @@ def test_signatures_match_the_reference(ref_modules):
     for name, ours in patch._NAMES.items():
         ref = getattr(utils, name, None) or getattr(scvf, name, None) or \
             getattr(ref_modules["dynamo.prediction.utils"], name, None) or \
-            getattr(ref_modules["dynamo.prediction.fate"], name, None)
+            getattr(ref_modules["dynamo.prediction.fate"], name, None) or \
+            getattr(ref_modules["dynamo.vectorfield.rank_vf"], name, None)
         assert ref is not None, name
         if inspect.isclass(ref):
             ref, ours = ref.__init__, ours.__init__
