@@ -15,7 +15,8 @@ def ref_modules():
     ref_loader.install()
     mods = {m: ref_loader.load(m) for m in ("dynamo.vectorfield.utils", "dynamo.vectorfield.scVectorField",
                                             "dynamo.vectorfield.vector_calculus", "dynamo.vectorfield.VectorField",
-                                            "dynamo.vectorfield.rank_vf", "dynamo.prediction.utils")}
+                                            "dynamo.vectorfield.rank_vf", "dynamo.prediction.utils",
+                                            "dynamo.vectorfield.least_action_path")}
     import sys
     sys.modules["dynamo.vectorfield"].vector_field_function = mods["dynamo.vectorfield.utils"].vector_field_function
     mods["dynamo.prediction.fate"] = ref_loader.load("dynamo.prediction.fate")
@@ -35,7 +36,8 @@ def test_signatures_match_the_reference(ref_modules):
         ref = getattr(utils, name, None) or getattr(scvf, name, None) or \
             getattr(ref_modules["dynamo.prediction.utils"], name, None) or \
             getattr(ref_modules["dynamo.prediction.fate"], name, None) or \
-            getattr(ref_modules["dynamo.vectorfield.rank_vf"], name, None)
+            getattr(ref_modules["dynamo.vectorfield.rank_vf"], name, None) or \
+            getattr(ref_modules["dynamo.vectorfield.least_action_path"], name, None)
         assert ref is not None, name
         if inspect.isclass(ref):
             ref, ours = ref.__init__, ours.__init__
