@@ -282,6 +282,162 @@ __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64
     }
 }
 
+// K7 v3 (D <= 32): the kernel values of pass 1 stay ON CHIP for pass 2.  k_dac recomputes |x - c|^2 and exp in its second
+// pass (118 of its 300 FP64 instructions per cell and control point; parking k in HBM was slower).  Here a CTA owns CC
+// cells and Q threads share a cell, each taking every Q-th control point: the CC x M kernel values fit in shared memory
+// (32 cells x 512 control points = 128 KB), x / partial v / partial a stay in registers, and the partial sums are
+// combined with log2(Q) shuffles per dimension.  Pass 2 needs only  s_m = (x - c_m) . v = (x - s) . v - (c_m - s) . v
+// (s = the first control point: any shift is algebraically exact and keeps both terms at the scale of the data
+// spread), i.e. ONE fma per dimension, then a += (k_m s_m) C_m: 2 D instead of 4 D + exp.
+// Per cell and control point: pass 1 4 D + exp, pass 2 2 D  ->  ~6 D + 20 = 212 FP64 instructions at D = 32 (was 300).
+template <int DP, int CC, int Q>
+__global__ void __launch_bounds__(CC * Q) k_dac3(const double* __restrict__ x, int64_t n, int D,
+                                                 const double* __restrict__ Xc, int M, int Mp, double beta,
+                                                 const double* __restrict__ C, int formula, double* __restrict__ v_out,
+                                                 double* __restrict__ div_out, double* __restrict__ acc_out,
+                                                 double* __restrict__ accn_out, double* __restrict__ curv_out,
+                                                 double* __restrict__ curvn_out) {
+    constexpr int LDR = DP + 2;          // padded row: Q consecutive rows fall into distinct banks
+    constexpr int MC = 64;               // control points per staged chunk
+    extern __shared__ double sm3[];
+    double* cs = sm3;                    // [MC][LDR]  control points (pass 2: minus the shift)
+    double* Cs = cs + MC * LDR;          // [MC][LDR]  coefficients
+    double* ks = Cs + MC * LDR;          // [CC][Mp]   kernel values of this CTA's cells
+    const int tid = threadIdx.x, cl = tid / Q, q = tid % Q;
+    const int64_t cell = (int64_t)blockIdx.x * CC + cl;
+    const bool live = cell < n;
+    double xr[DP], vr[DP];
+#pragma unroll
+    for (int d = 0; d < DP; ++d) { xr[d] = (live && d < D) ? x[cell * D + d] : 0.0; vr[d] = 0.0; }
+    double div = 0.0;
+    double* kcell = ks + (size_t)cl * Mp;
+    auto stage = [&](int m0, int mc, bool shifted) {
+        __syncthreads();
+        for (int e = tid; e < mc * DP; e += CC * Q) {
+            const int r = e / DP, d = e % DP;
+            const bool ok = d < D;
+            const double c = ok ? Xc[(int64_t)(m0 + r) * D + d] : 0.0;
+            cs[r * LDR + d] = (shifted && ok) ? c - Xc[d] : c;
+            Cs[r * LDR + d] = ok ? C[(int64_t)(m0 + r) * D + d] : 0.0;
+        }
+        __syncthreads();
+    };
+    // pass 1: k_m (kept), v = sum_m k_m C_m, div = -2 beta sum_m k_m C_m . (x - c_m)
+    for (int m0 = 0; m0 < M; m0 += MC) {
+        const int mc = min(MC, M - m0);
+        stage(m0, mc, false);
+        for (int mm = q; mm < mc; mm += Q) {
+            const double* cr = cs + mm * LDR;
+            const double* Cr = Cs + mm * LDR;
+            double d2a = 0.0, d2b = 0.0, t2a = 0.0, t2b = 0.0;
+#pragma unroll
+            for (int d = 0; d < DP; d += 2) {
+                const double ta = xr[d] - cr[d], tb = xr[d + 1] - cr[d + 1];
+                d2a = fma(ta, ta, d2a);
+                d2b = fma(tb, tb, d2b);
+                t2a = fma(ta, Cr[d], t2a);
+                t2b = fma(tb, Cr[d + 1], t2b);
+            }
+            const double k = exp(-beta * (d2a + d2b));
+            kcell[m0 + mm] = k;
+            div = fma(k, t2a + t2b, div);
+#pragma unroll
+            for (int d = 0; d < DP; ++d) vr[d] = fma(k, Cr[d], vr[d]);
+        }
+    }
+#pragma unroll
+    for (int o = 1; o < Q; o <<= 1) {
+        div += __shfl_xor_sync(0xffffffffu, div, o);
+#pragma unroll
+        for (int d = 0; d < DP; ++d) vr[d] += __shfl_xor_sync(0xffffffffu, vr[d], o);
+    }
+    div *= -2.0 * beta;
+    const bool need_acc = acc_out || accn_out || curv_out || curvn_out;
+    double ar[DP];
+#pragma unroll
+    for (int d = 0; d < DP; ++d) ar[d] = 0.0;
+    if (need_acc) {
+        // pass 2: a = J v = -2 beta sum_m k_m s_m C_m,  s_m = (x - s) . v - (c_m - s) . v
+        double xv = 0.0;
+#pragma unroll
+        for (int d = 0; d < DP; ++d) xv = fma((d < D) ? xr[d] - Xc[d] : 0.0, vr[d], xv);
+        for (int m0 = 0; m0 < M; m0 += MC) {
+            const int mc = min(MC, M - m0);
+            stage(m0, mc, true);
+            for (int mm = q; mm < mc; mm += Q) {
+                const double* cr = cs + mm * LDR;
+                const double* Cr = Cs + mm * LDR;
+                double sa = 0.0, sb = 0.0;
+#pragma unroll
+                for (int d = 0; d < DP; d += 2) {
+                    sa = fma(cr[d], vr[d], sa);
+                    sb = fma(cr[d + 1], vr[d + 1], sb);
+                }
+                const double ksm = kcell[m0 + mm] * (xv - (sa + sb));
+#pragma unroll
+                for (int d = 0; d < DP; ++d) ar[d] = fma(ksm, Cr[d], ar[d]);
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < Q; o <<= 1) {
+#pragma unroll
+            for (int d = 0; d < DP; ++d) ar[d] += __shfl_xor_sync(0xffffffffu, ar[d], o);
+        }
+#pragma unroll
+        for (int d = 0; d < DP; ++d) ar[d] *= -2.0 * beta;
+    }
+    if (!live) return;
+    // every one of the Q threads of a cell now holds the complete v (and a); thread q writes the dimensions d = q (mod Q)
+    if (v_out) {
+#pragma unroll
+        for (int d = 0; d < DP; ++d)
+            if (d < D && (d % Q) == q) v_out[cell * D + d] = vr[d];
+    }
+    if (div_out && q == 0) div_out[cell] = div;
+    if (!need_acc) return;
+    double vv = 0.0, va = 0.0, aa = 0.0;
+#pragma unroll
+    for (int d = 0; d < DP; ++d) { vv = fma(vr[d], vr[d], vv); va = fma(vr[d], ar[d], va); aa = fma(ar[d], ar[d], aa); }
+    if (acc_out) {
+#pragma unroll
+        for (int d = 0; d < DP; ++d)
+            if (d < D && (d % Q) == q) acc_out[cell * D + d] = ar[d];
+    }
+    if (accn_out && q == 0) accn_out[cell] = sqrt(aa);
+    if (formula == 2) {
+        const double nv = sqrt(vv);
+        const double den = (nv * nv) * (nv * nv);
+        double kk = 0.0;
+#pragma unroll
+        for (int d = 0; d < DP; ++d) {
+            const double c = (ar[d] * vv - vr[d] * va) / den;   // padded dims: a = v = 0 -> c = 0
+            if (curv_out && d < D && (d % Q) == q) curv_out[cell * D + d] = c;
+            kk = fma(c, c, kk);
+        }
+        if (curvn_out && q == 0) curvn_out[cell] = sqrt(kk);
+    } else if (curvn_out && q == 0) {
+        const double nv = sqrt(vv);
+        curvn_out[cell] = sqrt(vv * aa) / (nv * nv * nv);
+    }
+}
+
+template <int DP, int CC, int Q>
+static int launch_dac3(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
+                       int formula, double* v, double* div, double* acc, double* acc_norm, double* curv,
+                       double* curv_norm, cudaStream_t st) {
+    const int Mp = ((M + 15) / 16) * 16 + 8;      // == 8 (mod 16): the cells of a warp hit different banks
+    const size_t smem = sizeof(double) * (2 * (size_t)64 * (DP + 2) + (size_t)CC * Mp);
+    static size_t attr = 0;
+    if (smem > attr) {
+        DVF_CUDA(cudaFuncSetAttribute(k_dac3<DP, CC, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr = smem;
+    }
+    k_dac3<DP, CC, Q><<<(unsigned)((n + CC - 1) / CC), CC * Q, smem, st>>>(x, n, D, Xc, M, Mp, beta, C, formula, v, div, acc,
+                                                                        acc_norm, curv, curv_norm);
+    DVF_LAUNCH_CHECK();
+    return DVF_OK;
+}
+
 // Least-action-path terms (reference vectorfield/least_action_path.py:7-57): per path segment with centre x and
 // finite-difference velocity vp,   dv = vp - f(x)   and   z = dv J(x)   (the row-vector / Jacobian product action_grad needs),
 // without materialising J:  z_j = -2 beta sum_m k_m (dv . C_m) (x_j - c_mj).  Same skeleton as k_dac (one thread per point,
@@ -575,6 +731,22 @@ extern "C" int dvf_div_acc_curv(const double* x, int64_t n, int D, const double*
         else launch(std::integral_constant<int, 32>());
         DVF_LAUNCH_CHECK();
         return DVF_OK;
+    }
+    // v3 (kernel values kept on chip between the passes) is correct but MEASURED SLOWER on B200 (1M x 30, M = 500: 26.0 ms
+    // against 11.5 ms): with Q threads per cell a staged chunk of 64 control points is consumed 8x faster, so the
+    // unoverlapped staging (two block barriers + the global loads, one CTA per SM) dominates.  It stays behind
+    // DVF_DAC_V3=1 until the staging is double-buffered.
+    static const bool v3 = getenv("DVF_DAC_V3") && atoi(getenv("DVF_DAC_V3")) != 0;
+    const bool want_acc = acc || acc_norm || curv || curv_norm;
+    if (v3 && want_acc && M >= 64 && M <= 1024) {
+        return dispatch_dp(D, [&](auto dp) {
+            constexpr int DP = decltype(dp)::value;
+            if (M <= 512)
+                return launch_dac3<DP, 32, 8>(x, n, D, Xc, M, beta, C, formula, v, div, acc, acc_norm, curv, curv_norm,
+                                              (cudaStream_t)stream);
+            return launch_dac3<DP, 16, 16>(x, n, D, Xc, M, beta, C, formula, v, div, acc, acc_norm, curv, curv_norm,
+                                           (cudaStream_t)stream);
+        });
     }
     return dispatch_dp(D, [&](auto dp) {
         constexpr int DP = decltype(dp)::value;
