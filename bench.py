@@ -37,7 +37,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-GRAM_DRAM_BYTES_NCU = 4.85e9    # k_gram_parts: 4.84 GB read + 7 MB written per launch (ncu --set full, profiles/ncu_k_gram_parts_r01_details.txt)
+GRAM_DRAM_BYTES_NCU = 4.94e9    # k_gram_parts: 4.927 GB read + 9.6 MB written per launch (ncu --set full, profiles/ncu_k_gram_parts_r02_details.txt)
 FP64_PEAK_FALLBACK = 37.1       # DMMA m8n8k4 chain, profiles/fp64_peak_r01.json -- used only if tools/fp64_peak cannot run
 
 # cells, D, M, MaxIter, ecr, EM iterations the full-size GPU job executes (reference-arm rescale target), default scaling
@@ -73,6 +73,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-variants", action="store_true", help="skip the timing of the other M x M solver (ncu runs)")
     a = ap.parse_args()
     w = WORKLOADS[a.workload]
     for k in ("cells", "pcs", "ctrl", "maxiter", "ecr"):
@@ -454,20 +455,21 @@ def run_ours(a):
     variants = {}
     other = "cholesky" if a.lstsq == "drouin" else "drouin"
     em2 = dict(em, solver=solver_code(other))
-    step_device(em2)
-    barrier()
-    v0, v1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    v0.record()
-    for _ in range(2):
+    if not a.no_variants:
         step_device(em2)
-    v1.record()
-    barrier()
-    tv = torch.tensor([v0.elapsed_time(v1) / 2], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(tv, op=dist.ReduceOp.MAX)
-    variants["lstsq_method=" + other] = {"value": n_tot / (float(tv.item()) * 1e-3), "ms_per_step": float(tv.item()),
-                                         "em_iterations": state["n_iter"], "sigma2": state["sigma2"], "steps": 2}
-    state.update(main_state)
+        barrier()
+        v0, v1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        v0.record()
+        for _ in range(2):
+            step_device(em2)
+        v1.record()
+        barrier()
+        tv = torch.tensor([v0.elapsed_time(v1) / 2], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tv, op=dist.ReduceOp.MAX)
+        variants["lstsq_method=" + other] = {"value": n_tot / (float(tv.item()) * 1e-3), "ms_per_step": float(tv.item()),
+                                             "em_iterations": state["n_iter"], "sigma2": state["sigma2"], "steps": 2}
+        state.update(main_state)
 
     # ---- parity of the benchmarked outputs (rank 0, single GPU) + sharded-vs-single parity (N > 1) ----
     parity = None

@@ -333,6 +333,20 @@ __device__ __forceinline__ unsigned long long lu_now() {
         }                                                                \
     } while (0)
 
+// 1 / x to within an ulp without the division's dependent chain of ~10 FP64 instructions and its slow-path branch:
+// hardware seed (MUFU.RCP64H, ~20 bits, full double range) + two Newton steps.  The panel computes it SPECULATIVELY for
+// every row's entry of the next column, so that it overlaps the arg-max reductions and the barrier and the winner's
+// reciprocal is simply picked (LAPACK getf2 also scales by the reciprocal of the pivot).
+__device__ __forceinline__ double lu_rcp(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    return r;
+}
+
 // shared state of the panel factorisation
 struct lu_panel_smem {
     double rowP[2][LU_NB];
@@ -340,7 +354,15 @@ struct lu_panel_smem {
     int wpos[2][LU_PWMAX], wown[2][LU_PWMAX];
     int s_piv[LU_NB];
     double U12s[LU_NB][LU_NB + 1];
+#ifdef DVF_LU_FINE
+    long long fine[8];
+#endif
 };
+#ifdef DVF_LU_FINE
+#define LU_FINE(slot) do { if (tid == 0) { const long long c__ = clock64(); sh.fine[slot] += c__ - fl; fl = c__; } } while (0)
+#else
+#define LU_FINE(slot) do { } while (0)
+#endif
 
 // Panel factorisation of the columns k0 .. k0 + 15 (rows k0 .. M - 1) by the first LU_PW warps of a CTA, R rows per thread
 // in registers, named barrier 1.  kprev >= 0: the trailing update of the PREVIOUS panel (columns kprev .. kprev + 15) has
@@ -353,6 +375,9 @@ __device__ __forceinline__ void lu_panel(const lu_args& a, int k0, int kprev, lu
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nbe = min(LU_NB, M - k0);
     double* N = a.N;
+#ifdef DVF_LU_FINE
+    long long fl = clock64();
+#endif
     constexpr int PT = LU_PW * 32;
     double av[R][LU_NB];
     int pos[R];
@@ -388,8 +413,11 @@ __device__ __forceinline__ void lu_panel(const lu_args& a, int k0, int kprev, lu
     for (int j = 0; j < LU_NB; ++j) {
         if (j < nbe) {                     // uniform over the panel warps
             const int par = j & 1;
-            // arg-max of |column j| over the rows not yet eliminated: the magnitude first (5 shuffles), then the
-            // smallest logical row among the lanes that hold it (one ballot unless magnitudes tie)
+            LU_FINE(0);      // previous column's elimination (+ the panel load for j = 0)
+            // arg-max of |column j| over the rows not yet eliminated.  |v| >= 0, so the bit pattern orders like the
+            // value: two 32-bit warp reductions (REDUX.MAX: high word, then low word among the lanes that hold the
+            // largest high word) instead of five 64-bit shuffle steps; ties in magnitude go to the smallest logical row
+            // (LAPACK's idamax takes the first)
             double bv = -1.0, bs = 0.0;
             int bp = NOROW, bo = 0;
 #pragma unroll
@@ -399,32 +427,45 @@ __device__ __forceinline__ void lu_panel(const lu_args& a, int k0, int kprev, lu
                     bv = v; bs = av[q][j]; bp = pos[q]; bo = tid * R + q;
                 }
             }
-            double wv = bv;
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) wv = fmax(wv, __shfl_xor_sync(0xffffffffu, wv, o));
-            const unsigned eq = __ballot_sync(0xffffffffu, bv == wv && bp != NOROW);
-            if (__popc(eq) > 1) {          // tie in magnitude: LAPACK's idamax takes the first row
-                int mp = (bv == wv) ? bp : NOROW;
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) mp = min(mp, __shfl_xor_sync(0xffffffffu, mp, o));
-                const unsigned eq2 = __ballot_sync(0xffffffffu, bv == wv && bp == mp);
-                if (lane == __ffs(eq2) - 1) { sh.wval[par][warp] = bv; sh.wsgn[par][warp] = bs; sh.wpos[par][warp] = bp; sh.wown[par][warp] = bo; }
-            } else if (eq == 0) {          // no candidate in this warp (all its rows are eliminated / NaN)
-                if (lane == 0) { sh.wval[par][warp] = -1.0; sh.wsgn[par][warp] = 0.0; sh.wpos[par][warp] = NOROW; sh.wown[par][warp] = 0; }
-            } else if (lane == __ffs(eq) - 1) {
-                sh.wval[par][warp] = bv; sh.wsgn[par][warp] = bs; sh.wpos[par][warp] = bp; sh.wown[par][warp] = bo;
+            bs = lu_rcp(bs);       // speculative: the reciprocal of this thread's candidate (used only if it wins)
+            {
+                const bool cand = bp != NOROW && bv == bv;           // has a row, not NaN
+                const unsigned hi = cand ? (unsigned)__double2hiint(bv) : 0u, lo = (unsigned)__double2loint(bv);
+                const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+                const bool top = cand && hi == mh;
+                const unsigned ml = __reduce_max_sync(0xffffffffu, top ? lo : 0u);
+                const bool win = top && lo == ml;
+                const unsigned mp = __reduce_min_sync(0xffffffffu, win ? (unsigned)bp : 0xffffffffu);
+                const unsigned who = __ballot_sync(0xffffffffu, win && (unsigned)bp == mp);
+                if (who == 0u) {           // no candidate in this warp (all its rows are eliminated / NaN)
+                    if (lane == 0) { sh.wval[par][warp] = -1.0; sh.wsgn[par][warp] = 0.0; sh.wpos[par][warp] = NOROW; sh.wown[par][warp] = 0; }
+                } else if (lane == __ffs(who) - 1) {
+                    sh.wval[par][warp] = bv; sh.wsgn[par][warp] = bs; sh.wpos[par][warp] = bp; sh.wown[par][warp] = bo;
+                }
             }
+            LU_FINE(1);      // arg-max inside the warp
             asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
-            bv = -1.0; bs = 0.0; bp = NOROW; bo = 0;
-#pragma unroll
-            for (int w = 0; w < LU_PW; ++w) {   // broadcast reads; every thread scans the LU_PW candidates
-                const double v = sh.wval[par][w];
-                const int p2 = sh.wpos[par][w];
-                if (v > bv || (v == bv && p2 < bp)) { bv = v; bs = sh.wsgn[par][w]; bp = p2; bo = sh.wown[par][w]; }
+            LU_FINE(2);      // barrier 1
+            {   // the LU_PW warp candidates: lane w < LU_PW takes candidate w, the same three reductions, then the winner's
+                // fields are broadcast with shuffles (every warp does this redundantly; no second barrier for it)
+                const int w = lane < LU_PW ? lane : 0;
+                const double cv = sh.wval[par][w];
+                const double cs_ = sh.wsgn[par][w];
+                const int cp = sh.wpos[par][w], co = sh.wown[par][w];
+                const bool cand = lane < LU_PW && cp != NOROW && cv >= 0.0;
+                const unsigned hi = cand ? (unsigned)__double2hiint(cv) : 0u, lo = (unsigned)__double2loint(cv);
+                const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+                const bool top = cand && hi == mh;
+                const unsigned ml = __reduce_max_sync(0xffffffffu, top ? lo : 0u);
+                const bool win = top && lo == ml;
+                const unsigned mp = __reduce_min_sync(0xffffffffu, win ? (unsigned)cp : 0xffffffffu);
+                const unsigned who = __ballot_sync(0xffffffffu, win && (unsigned)cp == mp);
+                const int src = who ? __ffs(who) - 1 : 0;
+                bv = who ? __shfl_sync(0xffffffffu, cv, src) : -1.0;
+                bs = __shfl_sync(0xffffffffu, cs_, src);
+                bp = who ? __shfl_sync(0xffffffffu, cp, src) : NOROW;
+                bo = __shfl_sync(0xffffffffu, co, src);
             }
-            // LAPACK getf2 scales the column by the reciprocal of the pivot (|pivot| >= sfmin); the division
-            // runs while the pivot row travels through shared memory
-            const double rpv = 1.0 / bs;
             if (tid == 0) {
                 sh.s_piv[j] = bp;
                 if (!(bv > 0.0)) atomicCAS(a.info, 0, k0 + j + 1);      // exactly singular (or NaN)
@@ -439,7 +480,10 @@ __device__ __forceinline__ void lu_panel(const lu_args& a, int k0, int kprev, lu
                     pos[q] = bp;                     // the row that sat at k0 + j goes where the pivot row was
                 }
             }
+            const double rpv = bs;     // the winner's reciprocal, computed before the reductions
+            LU_FINE(3);      // scan of the warp candidates, reciprocal issued, pivot row to shared memory
             asm volatile("bar.sync 1, %0;" ::"n"(PT) : "memory");
+            LU_FINE(4);      // barrier 2
 #pragma unroll
             for (int q = 0; q < R; ++q) {
                 if (pos[q] != NOROW && pos[q] > k0 + j) {
@@ -472,6 +516,10 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
     __shared__ double Ps[LU_TR][LU_NB + 1];
     __shared__ double Qs[LU_NB][LU_TC];
     __shared__ lu_panel_smem sh;
+#ifdef DVF_LU_FINE
+    if (threadIdx.x < 8) sh.fine[threadIdx.x] = 0;
+    __syncthreads();
+#endif
     __shared__ int s_tp[2 * LU_NB], s_ts[2 * LU_NB], s_np;
     const int M = a.M, D = a.D, W = a.M + a.D, ldn = a.ldn;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -603,7 +651,7 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
                     double rdiag = 1.0;
 #pragma unroll
                     for (int jj = 0; jj < LU_NB; ++jj)
-                        if (jj == li) rdiag = 1.0 / useg[jj];
+                        if (jj == li) rdiag = lu_rcp(useg[jj]);
 #pragma unroll
                     for (int i = LU_NB - 1; i >= 0; --i) {
                         if (i < nbe) {                          // uniform over the warp
@@ -648,6 +696,9 @@ __global__ void __launch_bounds__(LU_THREADS) k_lu_factor(lu_args a) {
     if (tid == 0 && crank == 0) {
         unsigned long long* dbg = reinterpret_cast<unsigned long long*>(a.piv + 32);
         for (int i = 0; i < 8; ++i) dbg[i] = tacc[i];
+#ifdef DVF_LU_FINE
+        for (int i = 0; i < 8; ++i) dbg[8 + i] = (unsigned long long)sh.fine[i];
+#endif
     }
 }
 

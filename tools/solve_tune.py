@@ -39,6 +39,10 @@ def one(M, D, which):
         torch.cuda.synchronize()
         ldn = (M + D + 1) & ~1
         t = ws.view(torch.int64)[2 * M * ldn + 16: 2 * M * ldn + 24].cpu().numpy() / 1e3
+        fine = ws.view(torch.int64)[2 * M * ldn + 24: 2 * M * ldn + 32].cpu().numpy()
+        if fine.any():   # built with -DDVF_LU_FINE: cycles of thread 0 per section of the panel's column loop
+            print("   panel column loop (cycles per column): elimination %.0f | warp arg-max %.0f | barrier %.0f | scan + pivot row %.0f | barrier %.0f"
+                  % tuple(fine[:5] / M), flush=True)
         print("   factor phases (us): panel %.0f | sync %.0f | swaps+U12 %.0f | sync %.0f | trailing %.0f | sync %.0f | back-subst %.0f"
               % tuple(t[:7]), flush=True)
     print("%s M=%d D=%d grid=%s cluster=%s: %.3f ms per solve (incl. ~20 us host wrapper), info %d, rel. dev. from "
