@@ -79,6 +79,7 @@ SIGNATURES = {
     "dvf_solve_normal_workspace_bytes": (_i, [_i, _i, C.POINTER(_sz)]),
     "dvf_solve_normal": (_i, [_p, _i64, _p, _i, _i, _d, _p, _sz, _p, _p, _p]),
     "dvf_update_v": (_i, [_p, _p, _p, _d, _i64, _i, _i, _p, _p, _p, _p]),
+    "dvf_update_v_noalloc": (_i, [_p, _p, _p, _d, _i64, _i, _i, _p, _p, _p, _p]),
     "dvf_comm_unique_id": (_i, [_p]),
     "dvf_comm_init": (_i, [_p, _i, _i, C.POINTER(_p)]),
     "dvf_comm_destroy": (_i, [_p]),

@@ -273,3 +273,61 @@ extern "C" int dvf_update_v(const double* UY, const double* C, const double* P, 
     cudaFreeAsync(tmp, st);
     return rc;
 }
+
+// ---- allocation-free variant of dvf_update_v -----------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  dvf_update_v takes its scratch (the
+// zero-padded copy of C and the per-CTA partial sums) from the stream-ordered pool; here the same scratch lives in a
+// file-scope device array of a fixed, modest size that every GPU loading the library holds until exit:
+//   padded C : Mp x DP doubles, Mp = roundup(M, 32), DP = roundup(D, 8)  ->  M <= 1024, D <= 64  =  64 Ki doubles
+//   partials : one double per 128 cells                                   ->  N <= 4 194 304      =  32 Ki doubles
+// 768 KB in total.  Nothing in it has to start at zero: every word that is read was written earlier in the same call
+// (k_pad_c writes all Mp x DP entries, every CTA of k_update_v writes its partial), so the previous call's contents are
+// harmless.  All calls share the one array: calls that overlap on the GPU (different streams, or the same entry point
+// from two host threads) race -- serialise them.
+namespace dvf {
+constexpr int NA_MAX_M = 1024, NA_MAX_D = 64;
+constexpr int64_t NA_MAX_N = 4194304;
+constexpr size_t NA_C_DOUBLES = (size_t)NA_MAX_M * NA_MAX_D;                 // padded C
+constexpr size_t NA_PART_DOUBLES = (size_t)(NA_MAX_N / UV_CELLS);            // partial sums
+static __device__ __align__(256) double g_update_v_scratch[NA_C_DOUBLES + NA_PART_DOUBLES];
+
+// device address of the array on the CURRENT device, looked up once per device (in host code the array's name is only
+// a host-side stand-in, not a device address)
+static int update_v_scratch_ptr(double** out) {
+    constexpr int kMaxDev = 64;
+    static double* cache[kMaxDev] = {nullptr};
+    int dev = 0;
+    DVF_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDev) { set_error("device ordinal %d out of range", dev); return DVF_ERR_ARG; }
+    if (!cache[dev]) {
+        double* p = nullptr;
+        DVF_CUDA(cudaGetSymbolAddress((void**)&p, g_update_v_scratch));
+        cache[dev] = p;
+    }
+    *out = cache[dev];
+    return DVF_OK;
+}
+}  // namespace dvf
+
+extern "C" int dvf_update_v_noalloc(const double* UY, const double* C, const double* P, double minP, int64_t N, int D,
+                                    int M, double* V, double* r2, double* stats, void* stream) {
+    DVF_ARG(UY && C && P && r2 && stats && N >= 1 && M >= 1, "bad argument");
+    DVF_ARG(D >= 1 && D <= kMaxD, "D=%d unsupported (1..%d)", D, kMaxD);
+    if (M > NA_MAX_M || D > NA_MAX_D || N > NA_MAX_N) {
+        set_error("dvf_update_v_noalloc: fixed scratch serves M <= %d, D <= %d, N <= %lld (got M=%d D=%d N=%lld); use "
+                  "dvf_update_v", NA_MAX_M, NA_MAX_D, (long long)NA_MAX_N, M, D, (long long)N);
+        return DVF_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int Mp = (M + 31) / 32 * 32, DP = pad8(D);
+    const int64_t nb = updatev_blocks(N);
+    double* scratch = nullptr;
+    if (int rc = update_v_scratch_ptr(&scratch)) return rc;
+    double* Cp = scratch;                      // Mp * DP <= NA_C_DOUBLES
+    double* part = scratch + NA_C_DOUBLES;     // nb <= NA_PART_DOUBLES
+    int rc = pad_c_run(C, M, D, Cp, Mp, DP, nullptr, st);
+    if (!rc) rc = update_v_run(UY, Cp, P, minP, N, D, M, V, r2, part, nullptr, st);
+    if (!rc) rc = sum_partials_run(part, (int)nb, 1, stats, nullptr, st);
+    return rc;
+}

@@ -240,6 +240,14 @@ int dvf_gram(const double* UY, const double* P, double minP, int64_t N, int D, i
  * L: (M + D) x M scratch.  info (device int): 0 ok, k>0 = non-positive pivot at column k-1. */
 int dvf_solve(const double* G, int64_t ldg, const double* Kc, int M, int D, double lam_sigma2,
               double* L, double* C, int* info, void* stream);
+/* Allocation-free variant of dvf_update_v.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same arguments and results as dvf_update_v; the scratch (padded C + per-CTA partial sums, 768 KB) is a
+ * file-scope device array that every GPU loading the library holds until exit, so the call performs no cudaMalloc /
+ * cudaFree / pool allocation.  Limits: M <= 1024, D <= 64, N <= 4 194 304 -- beyond them DVF_ERR_WORKSPACE with a
+ * message.  All calls share the one array: calls that overlap on the GPU race, serialise them. */
+int dvf_update_v_noalloc(const double* UY, const double* C, const double* P, double minP, int64_t N, int D,
+                         int M, double* V, double* r2, double* stats, void* stream);
 /* The reference's solver form (DVF_SOLVER_NORMAL_LU) as a step: C = solve(lhs^T lhs, lhs^T rhs), LU with partial
  * pivoting (tools/utils.py:2975-2976 -> LAPACK gesv).  ws: dvf_solve_normal_workspace_bytes(); info: 0 ok, k>0 =
  * exactly zero pivot at column k-1 (numpy raises LinAlgError("Singular matrix") there). */
