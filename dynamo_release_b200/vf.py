@@ -101,16 +101,34 @@ class RkhsJacobian:
         return Jacobian_rkhs_gaussian(x, self.vf_dict, **{**self.kwargs, **kw})
 
 
+def _jacobian_out_dtype(x, vf_dict, single, vectorize):
+    """Result dtype of the reference for NumPy inputs: the per-cell loop writes into a float64 array (:368), but the
+    1-d path (:364-366) and the vectorised einsum (:374-377) return what `con_K(return_d=True)` produced, which does not
+    upcast (:199-205) -- float32 when x, X_ctrl and C all are.  The device computes in float64 either way; the result
+    is rounded to float32 there (the reference's float32 ARITHMETIC is not imitated: values agree to float32 rounding)."""
+    if not (single or vectorize):
+        return np.float64
+    parts = [x, vf_dict["X_ctrl"], vf_dict["C"]]
+    if isinstance(vf_dict["beta"], np.generic):
+        parts.append(vf_dict["beta"])          # a NumPy float64 scalar upcasts (NEP 50), a Python float does not
+    if all(isinstance(p, (np.ndarray, np.generic)) for p in parts):
+        return np.result_type(*parts, np.float32)
+    return np.float64
+
+
 def Jacobian_rkhs_gaussian(x, vf_dict, vectorize=False, device_out=False):
     """reference vectorfield/utils.py:351-379.  (D, D, n) for 2-d x, (D, D) for 1-d x."""
     Xc, beta, C = _vf_parts(vf_dict)
     x2, single = _as2d(x)
+    dt = np.float64 if device_out else _jacobian_out_dtype(x, vf_dict, single, vectorize)
     if not device_out and not single:
-        return kernels.jacobian_to_host(x2, Xc, beta, C)   # slabs stream to pinned host memory behind the GEMM
+        J = kernels.jacobian_to_host(x2, Xc, beta, C)      # slabs stream to pinned host memory behind the GEMM
+        return J if dt == np.float64 else J.astype(dt)
     J = kernels.jacobian(x2, Xc, beta, C)
     if single:
         J = J[:, :, 0]
-    return _out(J, device_out)
+    J = _out(J, device_out)
+    return J if (device_out or dt == np.float64) else J.astype(dt)
 
 
 def Jacobian_rkhs_gaussian_parallel(x, vf_dict, cores=None, device_out=False):

@@ -209,3 +209,32 @@ def test_svc_integrate_method(it):
     key = "sink/T3/forward/logspace/avg1"
     for i in range(len(Y)):
         assert rel(Y[i], z[f"{key}/Y{i}"]) < 1e-8
+
+
+def test_start_at_rest_and_leave_it_like_scipy(it):
+    """Round-1 advisor finding, on the device: the state starts just under the at-rest threshold next to an UNSTABLE fixed
+    point of an RKHS field, so the event function goes 0 -> -1 over the first accepted step.  scipy's find_active_events
+    fires on that too and brentq returns t_old: t = [t0, t0], y = [y0, y0], status 1 -- in both kernels (one trajectory
+    per CTA, and the lock-step kernel used for >= 8 states) exactly like solve_ivp itself."""
+    from scipy.integrate import solve_ivp
+
+    vf = {"X_ctrl": np.array([[-1.0, 0.0], [1.0, 0.0]]), "C": np.array([[-1.0, 0.0], [1.0, 0.0]]), "beta": 1.0}
+    f = lambda x: vo.field_eval(x, vf)  # noqa: E731
+    deltas = np.array([6.5e-6, 5e-6, 1e-6, -6.5e-6, 3e-2, 6.0e-6, 2e-6, 1e-1, 6.7e-6])   # 9 states -> lock-step kernel
+    y0 = np.stack([deltas, np.zeros_like(deltas)], 1)
+
+    def scipy_call(y):
+        ev = lambda t, x: np.all(abs(f(x)) < 1e-5) - 1  # noqa: E731  (prediction/utils.py:107)
+        ev.terminal = True
+        return solve_ivp(lambda t, x: f(x), [0.0, 20.0], y, events=ev, max_step=20.0, dense_output=True)
+
+    for states in (y0, y0[:3]):            # lock-step kernel, then one trajectory per CTA
+        res = it.solve_ivp_batch(states, vf, (0.0, 20.0), 20.0)
+        for r, y in zip(res, states):
+            g = scipy_call(y)
+            assert r.status == g.status, (y, r.status, g.status)
+            assert r.t.shape == g.t.shape, (y, r.t, g.t)
+            assert rel(r.t, g.t) < 1e-9 or np.array_equal(r.t, g.t)
+            assert np.max(np.abs(r.y - g.y)) <= 1e-9 * max(np.max(np.abs(g.y)), 1e-300)
+            if abs(y[0]) < 6.8e-6:         # started at rest: scipy stops at once, whether or not the first step leaves it
+                assert g.status == 1 and np.array_equal(r.t, [0.0, 0.0]) and np.array_equal(r.y[:, 0], r.y[:, 1])

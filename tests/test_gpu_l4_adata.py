@@ -199,6 +199,17 @@ def test_untested_surface_of_round_1(refmods, b200_backend):
     assert rel(dvf.vector_field_function(x, {"X_ctrl": y, "beta": 0.3, "C": y * 0.5}, timeit=True),
                vfu.vector_field_function(x, {"X_ctrl": y, "beta": 0.3, "C": y * 0.5}, timeit=True)) < 1e-13
 
+    # float32 inputs (utils.py:204-205: the return_d path does not upcast): dtypes as the reference, values to float32
+    vf32 = {"X_ctrl": y.astype(np.float32), "C": (y * 0.5).astype(np.float32), "beta": 0.3}
+    x32 = x.astype(np.float32)
+    for args, kw32 in (((x32[0],), {}), ((x32,), {}), ((x32,), {"vectorize": True}), ((x32.astype(np.float64),), {}),
+                       ((x32[0],), {"_beta": np.float64(0.3)})):
+        d32 = dict(vf32, beta=kw32.pop("_beta")) if "_beta" in kw32 else vf32
+        a, b = dvf.Jacobian_rkhs_gaussian(*args, d32, **kw32), vfu.Jacobian_rkhs_gaussian(*args, d32, **kw32)
+        assert a.dtype == b.dtype and a.shape == b.shape, (a.dtype, b.dtype, kw32)
+        assert rel(a, b) < 5e-6
+    assert dvf.vector_field_function(x32, vf32).dtype == vfu.vector_field_function(x32, vf32).dtype == np.float64
+
     X, V = o.hematopoiesis_like(1800, 30, seed=2)
     kw = dict(M=80, MaxIter=30, velocity_based_sampling=False, seed=3)
     ref = sc.SparseVFC(X, V, None, **kw)
