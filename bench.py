@@ -4,6 +4,7 @@
 Workloads (BASELINE.json configs; synthetic hematopoiesis-shaped cells):
   c3 (default, the one the metric is quoted on; fits one GPU): 1M cells x 30 PCs, M = 500 control points, MaxIter = 30
   c2: 100k x 30, M = 100          c5: 4M x 50, M = 1000, exactly 10 EM iterations (the all-reduce scaling sweep)
+  c4: the gene-space transform Q J Q^T at 200k cells x 50 PCs x 2000 genes (configs[3]; its own metric, run_c4)
 --scaling weak (default; what the driver's 1/2/4/8 run measures): every rank holds `cells` cells, ONE joint fit over
 N x cells (NCCL all-reduce of the Gram/RHS block per EM iteration), evaluation per rank.
 --scaling strong: `cells` is the TOTAL, split over the ranks (configs[2] "1M ... sharded across 8xB200", configs[4]).
@@ -48,6 +49,10 @@ WORKLOADS = {
                ref_fit=100_000, ref_eval=2_000),
     "c5": dict(cells=4_000_000, pcs=50, ctrl=1000, maxiter=10, ecr=0.0, iters_full={"drouin": 10, "cholesky": 10}, scaling="strong",
                ref_fit=12_000, ref_eval=400),
+    # configs[3]: gene-space Jacobian Q J Q^T, 200k cells x 50 PCs x 2000 genes (its own run function, run_c4; `ctrl` is
+    # the number of genes there)
+    "c4": dict(cells=200_000, pcs=50, ctrl=2000, maxiter=0, ecr=0.0, iters_full={"drouin": 0, "cholesky": 0}, scaling="weak",
+               ref_fit=0, ref_eval=48),
 }
 
 
@@ -612,9 +617,186 @@ def sharded_parity(a, dvf, comm, rank, world, n_total=200_000):
     return out if rank == 0 else None
 
 
+METRIC_C4 = "cells/sec for the gene-space Jacobian transform Q J Q^T (elementwise_jacobian_transformation family)"
+
+
+def c4_inputs(a, n, seed=2):
+    """seeded N(0,1) Jacobians (D, D, n), Q (genes x D) with orthonormal columns, 10 group labels."""
+    rng = np.random.default_rng(seed)
+    D, G = a.pcs, a.ctrl
+    Q, _ = np.linalg.qr(rng.normal(size=(G, D)))
+    J = rng.standard_normal((D, D, n))
+    lab = (np.arange(n) * 10 // max(n, 1)).astype(np.int32)
+    return J, np.ascontiguousarray(Q), lab
+
+
+def c4_reference(a, n_cells):
+    """The unmodified reference's subset_jacobian_transformation (utils.py:497-554, Python loop over cells) on n_cells."""
+    ref = CpuReference()
+    J, Q, _ = c4_inputs(a, n_cells)
+    if ref.kind == "reference":
+        fn = lambda: ref.vfu.subset_jacobian_transformation(J, Q, Q)   # noqa: E731
+    else:
+        fn = lambda: ref.o.gene_jacobian(J, Q, Q)                      # noqa: E731
+    t0 = time.perf_counter()
+    out = fn()
+    dt = time.perf_counter() - t0
+    return ref, n_cells / dt, dt, J, Q, out
+
+
+def run_c4_reference(a):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    vals, ms = [], []
+    for i in range(a.warmup + a.steps):
+        n = max(8, a.ref_eval // 4) if i < a.warmup else a.ref_eval
+        ref, rate, dt, *_ = c4_reference(a, n)
+        if i >= a.warmup:
+            vals.append(rate)
+            ms.append(dt * 1e3)
+    v = float(np.mean(vals))
+    sample = "%s: subset_jacobian_transformation on %d cells (%.2f s), linear in cells" % (ref.source, a.ref_eval, ms[-1] / 1e3)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC_C4, "value": v, "unit": "cells/s", "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": float(np.mean(ms)), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "c4: %d cells x %d PCs x %d genes, Q J Q^T -> float32" % (a.cells, a.pcs, a.ctrl)},
+        "cpu_baseline": {"value": v, "unit": "cells/s", "cores": os.cpu_count(), "kind": ref.kind, "sample": sample},
+        "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}), flush=True)
+
+
+def run_c4(a):
+    """configs[3].  `value`: Q_e J Q_r^T of all cells, J resident in HBM, the float32 (G, G, slab) result written into a
+    REUSED device slab (full write traffic, no retention: the whole output is 3.2 TB).  `e2e`: the variant
+    rank_jacobian_genes(abs=True, groups=...) consumes, through the public API: J from pinned host memory ->
+    average_jacobian_by_group -> (10, G, G) float64 means back on the host.  Cells shard over ranks without exchange."""
+    import torch
+    import torch.distributed as dist
+
+    import dynamo_release_b200 as dvf
+    from dynamo_release_b200 import _lib, kernels
+    from dynamo_release_b200.device import pinned_like
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = _lib.load()
+    N, D, G = a.cells, a.pcs, a.ctrl
+    peak, peak_detail = (measure_fp64_peak(local) if rank == 0 else (None, {}))
+    Jh, Q, lab = c4_inputs(a, N, seed=2 + rank)
+    Jh = pinned_like(Jh)
+    Jd = torch.from_numpy(Jh).cuda()
+    Qd = torch.from_numpy(Q).cuda()
+    slab = 2048
+    state = {}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        for c0 in range(0, N, slab):
+            out, _ = kernels.gene_transform(Jd[:, :, c0:c0 + slab].contiguous(), Qd, Qd)   # (G, G, <= slab) float32
+            state["last"] = (c0, out)
+
+    def step_e2e():
+        gm = dvf.average_jacobian_by_group(Jh, Q, Q, lab, 10, take_abs=True)
+        return Jh.nbytes, gm.nbytes
+
+    for _ in range(a.warmup):
+        step_device()
+    lib.dvf_profile_enable(1)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        step_device()
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    gram_ms, gram_n, launches = C.c_double(0), C.c_int(0), C.c_longlong(0)
+    lib.dvf_profile_get(C.byref(gram_ms), C.byref(gram_n), C.byref(launches))
+    lib.dvf_profile_enable(0)
+    t = torch.tensor([e0.elapsed_time(e1) / a.steps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    # parity (rank 0): the last slab's first cells against the executed reference, after the float32 cast
+    parity = None
+    if rank == 0 and not a.no_parity:
+        c0, out = state["last"]
+        k = min(a.ref_eval, out.shape[2])
+        ref = CpuReference()
+        Jsub = np.ascontiguousarray(Jh[:, :, c0:c0 + k])
+        want = (ref.vfu.subset_jacobian_transformation(Jsub, Q, Q) if ref.kind == "reference"
+                else ref.o.gene_jacobian(Jsub, Q, Q))
+        got = out[:, :, :k].cpu().numpy()
+        diff = np.abs(got.astype(np.float64) - want.astype(np.float64))
+        ulp = diff / np.maximum(np.spacing(np.abs(want)).astype(np.float64), 1e-45)
+        # an entry that cancels to ~1e-10 of its cell's scale carries the float64 rounding noise of the D^2-term contraction
+        # (~1e-17 here), which is several float32 steps of such a tiny value: those are judged against that noise instead
+        noise = 64 * 2.2e-16 * np.abs(want).max(axis=(0, 1), keepdims=True).astype(np.float64)
+        bad = (ulp > 1.0) & (diff > noise)
+        parity = {"against": ref.kind, "cells": int(k), "genes": [G, G], "dtype": str(got.dtype), "entries": int(ulp.size),
+                  "entries_differing": int((ulp > 0).sum()), "entries_beyond_1_ulp": int((ulp > 1.0).sum()),
+                  "max_ulp_float32": float(ulp.max()), "entries_beyond_1_ulp_and_beyond_f64_noise": int(bad.sum()),
+                  "gate": "every entry within 1 float32 ulp of the reference's, or within 64 eps64 x the cell's largest entry "
+                          "(float64 rounding noise of the contraction, for entries that cancel to ~0)",
+                  "pass": bool(not bad.any() and got.dtype == want.dtype)}
+    e2e = None
+    if not a.no_e2e:
+        h2d, d2h = step_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            h2d, d2h = step_e2e()
+        torch.cuda.synchronize()
+        te = torch.tensor([(time.perf_counter() - t0) / a.steps], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * N / float(te.item()), "unit": "cells/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": float(te.item()) * 1e3,
+               "note": "public API average_jacobian_by_group(|.|, 10 groups): pinned host J in, (10, G, G) float64 means out; "
+                       "the (G, G, n) array is never materialised"}
+    if rank == 0:
+        flops = 2.0 * G * D * (D + G) * N
+        achieved = flops / (ms * 1e-3) / 1e12
+        peak_used = peak if peak else FP64_PEAK_FALLBACK
+        line = {"metric": METRIC_C4, "value": world * N / (ms * 1e-3), "unit": "cells/s", "n_gpus": world, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "c4: %d cells x %d PCs x %d genes per GPU, Q J Q^T -> float32 (G, G, n) written into a "
+                                       "reused %d-cell device slab" % (N, D, G, slab),
+                           "l2": "inputs and outputs larger than L2 (J %.1f GB, slab %.1f GB)" % (Jd.numel() * 8 / 1e9, 4.0 * G * G * slab / 1e9),
+                           "parallelism": "cells sharded over %d GPU(s), no exchange" % world},
+                "clocks": clocks, "e2e": e2e, "parity": parity, "gpu_launches": int(launches.value),
+                "roofline": {"bound": "tensor", "kernel": "k_tsgemm x2 (two batched tall-skinny DGEMMs on FP64 DMMA fed by TMA) + "
+                             "the J slab copy, timed together over the step with CUDA events",
+                             "achieved": achieved, "peak": peak_used, "unit": "TFLOP/s", "frac": achieved / peak_used,
+                             "peak_measured_in_run": peak, "traffic": None,
+                             "algorithmic_flops_per_step": flops,
+                             "hbm_GBps_output": 4.0 * G * G * N / (ms * 1e-3) / 1e9}}
+        if not a.no_cpu_baseline and world == 1:
+            ref, rate, dt, *_ = c4_reference(a, a.ref_eval)
+            line["cpu_baseline"] = {"value": rate, "unit": "cells/s", "cores": os.cpu_count(), "kind": ref.kind,
+                                    "sample": "%s: subset_jacobian_transformation on %d cells (%.2f s), linear in cells"
+                                              % (ref.source, a.ref_eval, dt)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 if __name__ == "__main__":
     args = parse()
-    if args.impl == "reference":
+    if args.workload == "c4":
+        (run_c4_reference if args.impl == "reference" else run_c4)(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
