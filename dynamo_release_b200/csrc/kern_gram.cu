@@ -413,7 +413,13 @@ static double part_cost(const gram_tile& tl) { return kPartCost[tl.variant] * (t
 static void build_host_plan(int64_t N, int D, int M, int n_sms, gram_host_plan& hp) {
     read_tuning_env();
     const int units = (M + D + 7) / 8, nfull = units / 16, rt = units % 16;
-    auto add = [&](int v, int r0, int c0) { hp.tiles.push_back(gram_tile{v, r0, c0, (v == GV_HALF && r0 == c0) ? 1 : 0, 0}); };
+    // A tile whose rows AND columns all lie at or beyond M is part of the Y^T diag(P) Y block, which nothing reads (lhs is
+    // G[:M,:M], rhs is G[M:M+D,:M]): it is not computed.  At M = 500, D = 30 that is the last piece of the tail strip,
+    // 3072 of 154.6 k FMA per cell.
+    auto add = [&](int v, int r0, int c0) {
+        if (r0 >= M && c0 >= M) return;
+        hp.tiles.push_back(gram_tile{v, r0, c0, (v == GV_HALF && r0 == c0) ? 1 : 0, 0});
+    };
     for (int s = 0; s < nfull; ++s) {
         for (int jb = 0; jb < s; ++jb) add(GV_FULL, 128 * s, 128 * jb);
         add(GV_HALF, 128 * s, 128 * s);
