@@ -2,6 +2,7 @@
 // acceleration / curvature).  FP64 throughout; control points and coefficients are staged in shared
 // memory in chunks and broadcast to the threads, cells stream from HBM.
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace dvf {
 
@@ -290,42 +291,91 @@ __global__ void __launch_bounds__(128) k_dac(const double* __restrict__ x, int64
 // (s = the first control point: any shift is algebraically exact and keeps both terms at the scale of the data
 // spread), i.e. ONE fma per dimension, then a += (k_m s_m) C_m: 2 D instead of 4 D + exp.
 // Per cell and control point: pass 1 4 D + exp, pass 2 2 D  ->  ~6 D + 20 = 212 FP64 instructions at D = 32 (was 300).
+// Xcp = control points, Xcsp = control points minus the first one, Cpad = coefficients: each [M][DP], zero padded
+__global__ void k_pad_shift(const double* __restrict__ Xc, const double* __restrict__ C, int M, int D, int DP,
+                            double* __restrict__ Xcp, double* __restrict__ Xcsp, double* __restrict__ Cpad) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= M * DP) return;
+    const int m = e / DP, d = e % DP;
+    const bool ok = d < D;
+    const double c = ok ? Xc[(int64_t)m * D + d] : 0.0;
+    Xcp[e] = c;
+    Xcsp[e] = ok ? c - Xc[d] : 0.0;
+    Cpad[e] = ok ? C[(int64_t)m * D + d] : 0.0;
+}
+
 template <int DP, int CC, int Q>
 __global__ void __launch_bounds__(CC * Q) k_dac3(const double* __restrict__ x, int64_t n, int D,
-                                                 const double* __restrict__ Xc, int M, int Mp, double beta,
-                                                 const double* __restrict__ C, int formula, double* __restrict__ v_out,
+                                                 const double* __restrict__ Xcp, const double* __restrict__ Xcsp,
+                                                 const double* __restrict__ Cpad, int M, int Mp, double beta,
+                                                 int formula, double* __restrict__ v_out,
                                                  double* __restrict__ div_out, double* __restrict__ acc_out,
                                                  double* __restrict__ accn_out, double* __restrict__ curv_out,
                                                  double* __restrict__ curvn_out) {
-    constexpr int LDR = DP + 2;          // padded row: Q consecutive rows fall into distinct banks
+    // Thread layout: warp q (0..Q-1) x lane = cell (CC = 32).  All lanes of a warp read the SAME control point at the same
+    // time, so every shared-memory load is a broadcast (one wavefront); with Q adjacent lanes per cell (first version)
+    // each quarter-warp of an LDS.128 touched 8 different rows = 4 wavefronts per load and the kernel was bound by
+    // shared-memory bandwidth (23 ms).  The Q partial sums of v (and a) meet through shared memory.
+    static_assert(CC == 32, "one warp = 32 cells");
+    constexpr int LDR = DP;              // broadcast reads: no padding needed
     constexpr int MC = 64;               // control points per staged chunk
-    extern __shared__ double sm3[];
-    double* cs = sm3;                    // [MC][LDR]  control points (pass 2: minus the shift)
-    double* Cs = cs + MC * LDR;          // [MC][LDR]  coefficients
-    double* ks = Cs + MC * LDR;          // [CC][Mp]   kernel values of this CTA's cells
-    const int tid = threadIdx.x, cl = tid / Q, q = tid % Q;
+    constexpr int STG = 4 * MC * LDR;    // [2 stages][c | C][MC][LDR] doubles; also the Q x DP x CC reduction buffer
+    static_assert(STG >= Q * DP * CC, "reduction buffer must fit the staging area");
+    extern __shared__ __align__(128) double sm3[];
+    double* stg = sm3;
+    double* ks = stg + STG;              // [Mp][CC]   kernel values, cell fastest
+    const int tid = threadIdx.x, q = tid >> 5, cl = tid & 31;
     const int64_t cell = (int64_t)blockIdx.x * CC + cl;
     const bool live = cell < n;
-    double xr[DP], vr[DP];
+    double xr[DP], vr[DP], ar[DP];
 #pragma unroll
-    for (int d = 0; d < DP; ++d) { xr[d] = (live && d < D) ? x[cell * D + d] : 0.0; vr[d] = 0.0; }
-    double div = 0.0;
-    double* kcell = ks + (size_t)cl * Mp;
-    auto stage = [&](int m0, int mc, bool shifted) {
+    for (int d = 0; d < DP; ++d) { xr[d] = (live && d < D) ? x[cell * D + d] : 0.0; vr[d] = 0.0; ar[d] = 0.0; }
+    double div = 0.0, xv = 0.0;
+    const bool need_acc = acc_out || accn_out || curv_out || curvn_out;
+    const int nch = (M + MC - 1) / MC;
+    // sum of the Q partial vectors held in registers (w) -> every thread gets the complete vector back
+    auto reduce_q = [&](double (&w)[DP]) {
+        __syncthreads();                 // staging area free (pipeline drained by the caller)
+#pragma unroll
+        for (int d = 0; d < DP; ++d) stg[(q * DP + d) * CC + cl] = w[d];
         __syncthreads();
-        for (int e = tid; e < mc * DP; e += CC * Q) {
-            const int r = e / DP, d = e % DP;
-            const bool ok = d < D;
-            const double c = ok ? Xc[(int64_t)(m0 + r) * D + d] : 0.0;
-            cs[r * LDR + d] = (shifted && ok) ? c - Xc[d] : c;
-            Cs[r * LDR + d] = ok ? C[(int64_t)(m0 + r) * D + d] : 0.0;
+#pragma unroll
+        for (int d = 0; d < DP; ++d) {
+            double acc = 0.0;
+#pragma unroll
+            for (int qq = 0; qq < Q; ++qq) acc += stg[(qq * DP + d) * CC + cl];
+            w[d] = acc;
         }
+        fence_proxy_async_smem();
         __syncthreads();
     };
-    // pass 1: k_m (kept), v = sum_m k_m C_m, div = -2 beta sum_m k_m C_m . (x - c_m)
-    for (int m0 = 0; m0 < M; m0 += MC) {
-        const int mc = min(MC, M - m0);
-        stage(m0, mc, false);
+    // Staging: the control points, the shifted control points and the coefficients come PRE-PADDED to DP columns from a
+    // global scratch (k_pad_shift), so a chunk of MC rows is one contiguous block and ONE thread stages it with two TMA
+    // bulk copies that complete on an mbarrier; the compute warps never execute copy code.  Global chunk counter g:
+    // stage g & 1, barrier phase (g >> 1) & 1.  A stage is refilled only after the block barrier that ends its use, and
+    // generic-proxy accesses are fenced before the async-proxy write (see kern_gram.cu).
+    __shared__ __align__(8) uint64_t full[2];
+    if (tid == 0) { mbar_init(&full[0], 1); mbar_init(&full[1], 1); mbar_fence_init(); }
+    __syncthreads();
+    auto issue = [&](int g, const double* cbase, int t) {           // chunk t of the pass whose control points are cbase
+        if (tid == 0) {
+            const int m0 = t * MC, mc = min(MC, M - m0);
+            const unsigned bytes = (unsigned)(mc * DP * sizeof(double));
+            double* cdst = stg + (g & 1) * (2 * MC * LDR);
+            mbar_arrive_expect_tx(&full[g & 1], 2 * bytes);
+            bulk_g2s(cdst, cbase + (int64_t)m0 * DP, bytes, &full[g & 1]);
+            bulk_g2s(cdst + MC * LDR, Cpad + (int64_t)m0 * DP, bytes, &full[g & 1]);
+        }
+    };
+    int g = 0;
+    // ---- pass 1: k_m (kept on chip), v = sum_m k_m C_m, div = -2 beta sum_m k_m C_m . (x - c_m) ----
+    issue(g, Xcp, 0);
+    for (int t = 0; t < nch; ++t, ++g) {
+        if (t + 1 < nch) issue(g + 1, Xcp, t + 1);                  // the next chunk travels while this one is consumed
+        mbar_wait(&full[g & 1], (g >> 1) & 1);
+        const double* cs = stg + (g & 1) * (2 * MC * LDR);
+        const double* Cs = cs + MC * LDR;
+        const int m0 = t * MC, mc = min(MC, M - m0);
         for (int mm = q; mm < mc; mm += Q) {
             const double* cr = cs + mm * LDR;
             const double* Cr = Cs + mm * LDR;
@@ -339,31 +389,36 @@ __global__ void __launch_bounds__(CC * Q) k_dac3(const double* __restrict__ x, i
                 t2b = fma(tb, Cr[d + 1], t2b);
             }
             const double k = exp(-beta * (d2a + d2b));
-            kcell[m0 + mm] = k;
+            ks[(m0 + mm) * CC + cl] = k;
             div = fma(k, t2a + t2b, div);
 #pragma unroll
             for (int d = 0; d < DP; ++d) vr[d] = fma(k, Cr[d], vr[d]);
         }
+        fence_proxy_async_smem();
+        __syncthreads();                 // this stage may be refilled by the copy issued in the next iteration
     }
+    reduce_q(vr);
+    {   // div: Q partials through the same buffer
+        stg[q * CC + cl] = div;
+        __syncthreads();
+        div = 0.0;
 #pragma unroll
-    for (int o = 1; o < Q; o <<= 1) {
-        div += __shfl_xor_sync(0xffffffffu, div, o);
-#pragma unroll
-        for (int d = 0; d < DP; ++d) vr[d] += __shfl_xor_sync(0xffffffffu, vr[d], o);
+        for (int qq = 0; qq < Q; ++qq) div += stg[qq * CC + cl];
+        fence_proxy_async_smem();
+        __syncthreads();
     }
     div *= -2.0 * beta;
-    const bool need_acc = acc_out || accn_out || curv_out || curvn_out;
-    double ar[DP];
-#pragma unroll
-    for (int d = 0; d < DP; ++d) ar[d] = 0.0;
     if (need_acc) {
-        // pass 2: a = J v = -2 beta sum_m k_m s_m C_m,  s_m = (x - s) . v - (c_m - s) . v
-        double xv = 0.0;
+        // ---- pass 2: a = J v = -2 beta sum_m k_m s_m C_m,  s_m = (x - s) . v - (c_m - s) . v  (Xcsp = c - s) ----
 #pragma unroll
-        for (int d = 0; d < DP; ++d) xv = fma((d < D) ? xr[d] - Xc[d] : 0.0, vr[d], xv);
-        for (int m0 = 0; m0 < M; m0 += MC) {
-            const int mc = min(MC, M - m0);
-            stage(m0, mc, true);
+        for (int d = 0; d < DP; ++d) xv = fma((live && d < D) ? xr[d] - Xcp[d] : 0.0, vr[d], xv);
+        issue(g, Xcsp, 0);
+        for (int t = 0; t < nch; ++t, ++g) {
+            if (t + 1 < nch) issue(g + 1, Xcsp, t + 1);
+            mbar_wait(&full[g & 1], (g >> 1) & 1);
+            const double* cs = stg + (g & 1) * (2 * MC * LDR);
+            const double* Cs = cs + MC * LDR;
+            const int m0 = t * MC, mc = min(MC, M - m0);
             for (int mm = q; mm < mc; mm += Q) {
                 const double* cr = cs + mm * LDR;
                 const double* Cr = Cs + mm * LDR;
@@ -373,16 +428,14 @@ __global__ void __launch_bounds__(CC * Q) k_dac3(const double* __restrict__ x, i
                     sa = fma(cr[d], vr[d], sa);
                     sb = fma(cr[d + 1], vr[d + 1], sb);
                 }
-                const double ksm = kcell[m0 + mm] * (xv - (sa + sb));
+                const double ksm = ks[(m0 + mm) * CC + cl] * (xv - (sa + sb));
 #pragma unroll
                 for (int d = 0; d < DP; ++d) ar[d] = fma(ksm, Cr[d], ar[d]);
             }
+            fence_proxy_async_smem();
+            __syncthreads();
         }
-#pragma unroll
-        for (int o = 1; o < Q; o <<= 1) {
-#pragma unroll
-            for (int d = 0; d < DP; ++d) ar[d] += __shfl_xor_sync(0xffffffffu, ar[d], o);
-        }
+        reduce_q(ar);
 #pragma unroll
         for (int d = 0; d < DP; ++d) ar[d] *= -2.0 * beta;
     }
@@ -425,16 +478,22 @@ template <int DP, int CC, int Q>
 static int launch_dac3(const double* x, int64_t n, int D, const double* Xc, int M, double beta, const double* C,
                        int formula, double* v, double* div, double* acc, double* acc_norm, double* curv,
                        double* curv_norm, cudaStream_t st) {
-    const int Mp = ((M + 15) / 16) * 16 + 8;      // == 8 (mod 16): the cells of a warp hit different banks
-    const size_t smem = sizeof(double) * (2 * (size_t)64 * (DP + 2) + (size_t)CC * Mp);
+    const int Mp = M;                             // ks is [M][CC], cell fastest
+    const size_t smem = sizeof(double) * (4 * (size_t)64 * DP + (size_t)CC * Mp);
     static size_t attr = 0;
     if (smem > attr) {
         DVF_CUDA(cudaFuncSetAttribute(k_dac3<DP, CC, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = smem;
     }
-    k_dac3<DP, CC, Q><<<(unsigned)((n + CC - 1) / CC), CC * Q, smem, st>>>(x, n, D, Xc, M, Mp, beta, C, formula, v, div, acc,
-                                                                        acc_norm, curv, curv_norm);
+    double* pad = nullptr;                        // [Xcp | Xcsp | Cpad], each M x DP, stream-ordered scratch
+    const size_t one = (size_t)M * DP;
+    DVF_CUDA(cudaMallocAsync(&pad, sizeof(double) * 3 * one, st));
+    k_pad_shift<<<(M * DP + 255) / 256, 256, 0, st>>>(Xc, C, M, D, DP, pad, pad + one, pad + 2 * one);
     DVF_LAUNCH_CHECK();
+    k_dac3<DP, CC, Q><<<(unsigned)((n + CC - 1) / CC), CC * Q, smem, st>>>(x, n, D, pad, pad + one, pad + 2 * one, M, Mp, beta,
+                                                                        formula, v, div, acc, acc_norm, curv, curv_norm);
+    DVF_LAUNCH_CHECK();
+    DVF_CUDA(cudaFreeAsync(pad, st));
     return DVF_OK;
 }
 
@@ -732,20 +791,20 @@ extern "C" int dvf_div_acc_curv(const double* x, int64_t n, int D, const double*
         DVF_LAUNCH_CHECK();
         return DVF_OK;
     }
-    // v3 (kernel values kept on chip between the passes) is correct but MEASURED SLOWER on B200 (1M x 30, M = 500: 26.0 ms
-    // against 11.5 ms): with Q threads per cell a staged chunk of 64 control points is consumed 8x faster, so the
-    // unoverlapped staging (two block barriers + the global loads, one CTA per SM) dominates.  It stays behind
-    // DVF_DAC_V3=1 until the staging is double-buffered.
+    // v3 (k_dac3: kernel values kept on chip between the passes, 212 instead of 300 FP64 instructions per cell and control
+    // point) is correct -- it agrees with k_dac to 5e-15 and passes the parity tests -- but MEASURED SLOWER on B200 in all
+    // three forms tried (1M x 30, M = 500; k_dac 12.0 ms): Q adjacent lanes per cell 26 ms -> with cp.async double
+    // buffering 23 ms (each quarter-warp of an LDS.128 touched 8 rows: 4 wavefronts per load) -> warp per q, lanes = cells
+    // (broadcast loads) 16.4 ms -> staging by one thread with TMA bulk copies from pre-padded scratch 15.8 ms.  What is
+    // left is the shared-memory -> register path: both passes load the same 2 x DP doubles per cell and control point, one
+    // use per loaded value, so halving the FP64 work of pass 2 does not shorten it.  It stays behind DVF_DAC_V3=1.
     static const bool v3 = getenv("DVF_DAC_V3") && atoi(getenv("DVF_DAC_V3")) != 0;
     const bool want_acc = acc || acc_norm || curv || curv_norm;
-    if (v3 && want_acc && M >= 64 && M <= 1024) {
+    if (v3 && want_acc && D >= 8 && M >= 64 && M <= 600) {       // DP >= 8: the reduction buffer fits the staging area
         return dispatch_dp(D, [&](auto dp) {
             constexpr int DP = decltype(dp)::value;
-            if (M <= 512)
-                return launch_dac3<DP, 32, 8>(x, n, D, Xc, M, beta, C, formula, v, div, acc, acc_norm, curv, curv_norm,
-                                              (cudaStream_t)stream);
-            return launch_dac3<DP, 16, 16>(x, n, D, Xc, M, beta, C, formula, v, div, acc, acc_norm, curv, curv_norm,
-                                           (cudaStream_t)stream);
+            return launch_dac3<DP, 32, 8>(x, n, D, Xc, M, beta, C, formula, v, div, acc, acc_norm, curv, curv_norm,
+                                          (cudaStream_t)stream);
         });
     }
     return dispatch_dp(D, [&](auto dp) {
