@@ -1,6 +1,7 @@
 // Error plumbing and ABI version of libdvf_b200.
 #include "common.cuh"
 #include "tma.cuh"
+#include "host_cumsum.h"
 #include <algorithm>
 #include <thread>
 #include <vector>
@@ -137,8 +138,7 @@ extern "C" int dvf_profile_get(double* gram_ms, int* gram_launches, long long* k
 // element-wise host passes of the sampling helper, split over a few threads once they are long enough to matter
 // (8M cells on rank 0 of an 8-GPU job); every element is computed exactly as the scalar loop would
 template <typename F>
-static void host_parallel_for(int64_t n, F body) {
-    const int64_t grain = 1 << 19;
+static void host_parallel_for(int64_t n, F body, int64_t grain = 1 << 19) {
     unsigned hw = std::thread::hardware_concurrency();
     int nt = (int)std::min<int64_t>(std::min<int64_t>(hw ? hw : 1, 8), (n + grain - 1) / grain);
     if (nt <= 1) { body((int64_t)0, n); return; }
@@ -160,8 +160,7 @@ extern "C" int dvf_host_scale(const double* v, int64_t n, double total, double* 
 // rounding of every partial sum matters to searchsorted) + one element-wise pass
 extern "C" int dvf_host_cdf(const double* p, int64_t n, double* cdf) {
     DVF_ARG(p && cdf && n >= 1, "bad argument");
-    double acc = 0.0;
-    for (int64_t i = 0; i < n; ++i) { acc += p[i]; cdf[i] = acc; }
+    dvf::host_scaled_cumsum(p, false, 1.0, nullptr, 0, cdf, n);
     const double tot = cdf[n - 1];
     host_parallel_for(n, [=](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) cdf[i] /= tot; });
     return DVF_OK;
@@ -211,12 +210,8 @@ extern "C" int dvf_host_pairwise_sum(const double* a, int64_t n, double* out) {
 extern "C" int dvf_host_choice_cumsum(const double* v, int64_t n, double total, const int64_t* skip, int64_t n_skip,
                                       double* raw) {
     DVF_ARG(v && raw && n >= 1 && (skip || n_skip == 0), "bad argument");
-    // the quotients are independent (threads); only the additions have to run one after the other
-    host_parallel_for(n, [=](int64_t a, int64_t b) { for (int64_t i = a; i < b; ++i) raw[i] = v[i] / total; });
-    for (int64_t s = 0; s < n_skip; ++s)
-        if (skip[s] >= 0 && skip[s] < n) raw[skip[s]] = 0.0;
-    double acc = 0.0;
-    for (int64_t i = 0; i < n; ++i) { acc += raw[i]; raw[i] = acc; }
+    // host_cumsum.cpp: quotients, zeroed entries and the additions, with the rounding of the sequential recurrence
+    dvf::host_scaled_cumsum(v, true, total, skip, n_skip, raw, n);
     return DVF_OK;
 }
 

@@ -75,3 +75,58 @@ def test_choice_input_validation_like_numpy():
     with pytest.raises(ValueError, match="Fewer non-zero"):
         prelude.velocity_weighted_choice(speed, 5, 0)
     assert sorted(prelude.velocity_weighted_choice(speed, 3, 0)) == [3, 7, 11]
+
+
+def _host_cumsum(v, total=1.0, skip=()):
+    import ctypes as C
+
+    from dynamo_release_b200 import _lib
+    v = np.ascontiguousarray(v, dtype=np.float64)
+    raw = np.empty_like(v)
+    sk = np.ascontiguousarray(sorted(skip), dtype=np.int64)
+    with np.errstate(all="ignore"):
+        _lib.check(_lib.load().dvf_host_choice_cumsum(v.ctypes.data_as(C.c_void_p), v.shape[0], float(total),
+                                                      sk.ctypes.data_as(C.c_void_p) if sk.size else None, sk.size,
+                                                      raw.ctypes.data_as(C.c_void_p)))
+    return raw
+
+
+def test_threaded_cumsum_is_numpy_cumsum_bit_for_bit():
+    """host_cumsum.cpp forms cumsum(speed / total) on several threads (exact block sums inside one binade + a serial
+    scan); every partial sum must carry the rounding of numpy's sequential recurrence, whatever the input looks like:
+    half-way cases, binade crossings, zeros at the head, an outlier, tiny / subnormal values, negative or non-finite
+    entries (the serial path), and the drawn cells zeroed through `skip`."""
+    rng = np.random.default_rng(0)
+    n = 700_003                          # 43 blocks of 16384 and a ragged tail
+    cases = {
+        "uniform": rng.random(n),
+        "norms": np.linalg.norm(rng.normal(size=(n, 4)), axis=1),
+        "lognormal": rng.lognormal(0, 5, n),
+        "integers": rng.integers(0, 1 << 20, n).astype(np.float64),                       # every sum exact, ties
+        "dyadic": rng.integers(0, 1 << 12, n).astype(np.float64) * 2.0 ** -40 + (rng.random(n) < 0.001) * 3.0,
+        "leading zeros": np.concatenate([np.zeros(100_000), rng.random(n - 100_000)]),
+        "mostly zeros": rng.random(n) * (rng.random(n) < 0.1),
+        "outlier": np.concatenate([rng.random(n // 2), [1e12], rng.random(n // 2)]),
+        "tiny": rng.random(n) * 1e-300,
+        "subnormal": rng.random(n) * 1e-315,
+        "negative": rng.normal(size=n),
+        "inf": np.concatenate([rng.random(n - 5), [np.inf], rng.random(4)]),
+        "halves": np.full(n, 0.5),
+        "half ulp": np.concatenate([[1.0], np.full(n - 1, 2.0 ** -53)]),                   # every step is a tie
+        "ulp mix": np.concatenate([[1.0], rng.choice([2.0 ** -53, 3 * 2.0 ** -53, 2.0 ** -52], n - 1)]),
+        "short": rng.random(1000),
+        "one": np.array([0.25]),
+    }
+    for name, v in cases.items():
+        with np.errstate(all="ignore"):
+            ref = np.cumsum(v)
+        got = _host_cumsum(v)
+        assert np.array_equal(ref.view(np.int64), got.view(np.int64)), name
+    # quotients and zeroed cells, as Generator.choice's second round sees them
+    v = cases["norms"]
+    total = float(np.sum(v))
+    skip = rng.choice(n, 300, replace=False)
+    p = v / total
+    p[skip] = 0.0
+    assert np.array_equal(np.cumsum(p), _host_cumsum(v, total, skip))
+    assert np.array_equal(np.cumsum(v / total), _host_cumsum(v, total))
