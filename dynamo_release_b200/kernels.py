@@ -320,7 +320,8 @@ def estep(r2, D, sigma2, gamma, a):
 
 
 def gram(UY, P, minP, D, M):
-    """scVectorField.py:468-476.  Returns G (ldg x ldg), lower-triangular tiles valid."""
+    """scVectorField.py:468-476.  Returns G (ldg x ldg): the lower triangle of columns < M is valid (U^T P U and
+    Y^T P U); the Y^T P Y corner is not computed."""
     UY = dev(UY)
     N = UY.shape[0]
     Pp = torch.zeros((N + 2,), dtype=torch.float64, device="cuda")

@@ -227,9 +227,11 @@ int dvf_build_uy(const double* X, const double* Y, int64_t N, int D, const doubl
  * sum P log(sigma2) D/2 (= E of get_P), sum P, min nonzero t1, number of exact zeros}. */
 int dvf_estep(const double* r2, int64_t N, int D, double sigma2, double gamma, double a, double* P,
               double* stats, void* stream);
-/* M-step assembly, scVectorField.py:468-476: G (W x W, lower triangle valid) = UY^T diag(max(P, minP)) UY.
+/* M-step assembly, scVectorField.py:468-476: G (W x W, lower triangle of the columns < M valid) = UY^T diag(max(P, minP)) UY.
  * scratch: dvf_gram_scratch_bytes(). */
 /* G is ldg x ldg with ldg = dvf_gram_ld(D, M) >= W (row-major; only lower-triangular tiles are written).
+ * Valid on return: G[i][j] for j <= i, j < M -- i.e. lhs' Gram part G[:M,:M] (lower triangle) and rhs^T = G[M:M+D,:M].
+ * The Y^T diag(P) Y block (i, j >= M) is read by nothing on the path and is left unspecified.
  * P must be 16-byte aligned and readable up to an even element count (allocate N + 1 doubles if N is odd). */
 int dvf_gram_ld(int D, int M);
 int dvf_gram_scratch_bytes(int64_t N, int D, int M, size_t* out);
