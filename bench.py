@@ -403,6 +403,8 @@ def run_ours(a):
             st = fit_em(Xv, Yv, ctrl, beta, workspace=state.get("ws"), **em)
             state["ws"] = st.workspace
         ev.append(mark())
+        ctrl = kernels.dev(ctrl)       # one upload of the control points for both evaluation calls: a pageable copy
+                                       # between them would make the host wait for the Jacobian before it can launch
         kernels.jacobian(Xd, ctrl, beta, st.C, out=J_buf)
         ev.append(mark())
         r = kernels.div_acc_curv(Xd, ctrl, beta, st.C, formula=2)
@@ -493,7 +495,7 @@ def run_ours(a):
     parity = None
     if rank == 0 and world == 1 and not a.no_parity:
         st = state["st"]
-        vf_fit = {"X_ctrl": np.asarray(state["ctrl"]), "beta": state["beta"], "C": st.C.cpu().numpy()}
+        vf_fit = {"X_ctrl": state["ctrl"].cpu().numpy(), "beta": state["beta"], "C": st.C.cpu().numpy()}
         try:
             parity = parity_block(a, dvf, np.ascontiguousarray(Xh[parity_cells]), vf_fit, parity_dev, n_fit=min(20_000, N))
         except Exception as e:   # the bench line must not be lost to a checker problem; say so instead
