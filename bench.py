@@ -38,7 +38,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-GRAM_DRAM_BYTES_NCU = 4.94e9    # k_gram_parts: 4.927 GB read + 9.6 MB written per launch (ncu --set full, profiles/ncu_k_gram_parts_r02_details.txt)
+GRAM_DRAM_BYTES_NCU = 4.615e9   # k_gram_parts: 4.608 GB read + 7.2 MB written per launch (ncu --set full, profiles/ncu_k_gram_parts_r02_details.txt)
 FP64_PEAK_FALLBACK = 37.1       # DMMA m8n8k4 chain, profiles/fp64_peak_r01.json -- used only if tools/fp64_peak cannot run
 
 # cells, D, M, MaxIter, ecr, EM iterations the full-size GPU job executes (reference-arm rescale target), default scaling
@@ -241,8 +241,12 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+            if os.environ.get("DVF_BENCH_SAMPLER") == "off":      # developer experiments only
+                raise RuntimeError("sampler disabled")
+            q = self.Q.replace("power.draw,", "") if os.environ.get("DVF_BENCH_SAMPLER") == "nopower" else self.Q
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms",
+                                          os.environ.get("DVF_BENCH_SAMPLER_MS", "100")], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -385,6 +389,8 @@ def run_ours(a):
         torch.cuda.synchronize()
 
     stage_ev = []
+    alloc_log = [] if os.environ.get("DVF_BENCH_HOSTLOG") else None
+    host_log = []      # host ms per step spent in: control-point upload, Jacobian call, div/acc/curv call (launches only)
 
     def mark():
         e = torch.cuda.Event(enable_timing=True)
@@ -393,6 +399,9 @@ def run_ours(a):
 
     def step_device(em=em):
         """whole job, inputs resident in HBM, results left in HBM"""
+        state.pop("st", None)          # the previous fit's V / P / C go back to the allocator before this step asks for
+                                       # its own: every step then issues the same allocation sequence and the caching
+                                       # allocator serves it without cudaMalloc (one per step otherwise, 1-90 ms of idle GPU)
         ev = [mark()]
         if world > 1:
             st, ctrl, _, beta, _ = fit_sharded(Xd, Vd, M, comm, **em)
@@ -400,15 +409,24 @@ def run_ours(a):
         else:
             _, Xv, Yv, ctrl, _, beta = prelude.run(Xd, Vd, M, seed=0)
             ev.append(mark())
+            if alloc_log is not None:
+                alloc_log.append(("prelude", torch.cuda.memory_stats().get("num_device_alloc", 0), torch.cuda.memory_reserved()))
             st = fit_em(Xv, Yv, ctrl, beta, workspace=state.get("ws"), **em)
             state["ws"] = st.workspace
+            if alloc_log is not None:
+                alloc_log.append(("fit", torch.cuda.memory_stats().get("num_device_alloc", 0), torch.cuda.memory_reserved()))
         ev.append(mark())
+        th = [time.perf_counter()]
         ctrl = kernels.dev(ctrl)       # one upload of the control points for both evaluation calls: a pageable copy
                                        # between them would make the host wait for the Jacobian before it can launch
+        th.append(time.perf_counter())
         kernels.jacobian(Xd, ctrl, beta, st.C, out=J_buf)
+        th.append(time.perf_counter())
         ev.append(mark())
-        r = kernels.div_acc_curv(Xd, ctrl, beta, st.C, formula=2)
+        r = kernels.div_acc_curv(Xd, ctrl, beta, st.C, formula=2, out=state.get("r"))   # outputs reused like J_buf
         ev.append(mark())
+        th.append(time.perf_counter())
+        host_log.append([round((th[i + 1] - th[i]) * 1e3, 2) for i in range(3)])
         stage_ev.append(ev)
         state.update(n_iter=st.n_iter, sigma2=st.sigma2, n_inlier=st.n_inlier, r=r, st=st, ctrl=ctrl, beta=beta)
 
@@ -441,6 +459,8 @@ def run_ours(a):
         step_device()
     lib.dvf_profile_enable(1)
     stage_ev.clear()
+    host_log.clear()
+    mem0 = torch.cuda.memory_stats()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -452,6 +472,18 @@ def run_ours(a):
     e1.record()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
+    mem1 = torch.cuda.memory_stats()
+    if rank == 0:
+        print("timed loop: host ms per step [ctrl upload, jacobian call, div/acc/curv call] max %s; driver allocations %d, "
+              "frees %d, retries %d" % ([max(h[i] for h in host_log) for i in range(3)],
+                                        mem1.get("num_device_alloc", 0) - mem0.get("num_device_alloc", 0),
+                                        mem1.get("num_device_free", 0) - mem0.get("num_device_free", 0),
+                                        mem1.get("num_alloc_retries", 0) - mem0.get("num_alloc_retries", 0)),
+              file=sys.stderr)
+        if os.environ.get("DVF_BENCH_HOSTLOG"):
+            print("host_log", host_log, file=sys.stderr)
+            print("alloc_log (stage, cudaMalloc count, reserved GB)", [(k, n, round(b / 1e9, 3)) for k, n, b in alloc_log[-16:]],
+                  file=sys.stderr)
     ms = e0.elapsed_time(e1) / a.steps
     gram_ms, gram_n, launches = C.c_double(0), C.c_int(0), C.c_longlong(0)
     lib.dvf_profile_get(C.byref(gram_ms), C.byref(gram_n), C.byref(launches))

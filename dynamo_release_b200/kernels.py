@@ -42,6 +42,26 @@ def eval_field(x, Xc, beta, Cm):
     return v
 
 
+_WS = {}
+
+
+def _workspace(nbytes):
+    """Scratch for the launch about to be issued on the current stream, kept per (device, stream) and grown on demand.
+    A fresh torch.empty per call looked free but was not: the caching allocator splits the released 0.5 GB block for
+    the next smaller request, so every other call went to cudaMalloc (1 ms, at times 60 ms of idle GPU -- measured
+    in bench.py's host log).  Calls on one stream are ordered, so they can share the buffer; release_workspaces()
+    gives the memory back."""
+    key = (torch.cuda.current_device(), stream_ptr())
+    ws = _WS.get(key)
+    if ws is None or ws.numel() * 8 < nbytes:
+        ws = _WS[key] = torch.empty((nbytes + 7) // 8, dtype=torch.float64, device="cuda")
+    return ws
+
+
+def release_workspaces():
+    _WS.clear()
+
+
 def jacobian(x, Xc, beta, Cm, out=None):
     """K6 -- reference vectorfield/utils.py:351-379; returns (D, D, n)."""
     x, Xc, Cm = _field(x, Xc, Cm)
@@ -50,8 +70,7 @@ def jacobian(x, Xc, beta, Cm, out=None):
     M = Xc.shape[0]
     nbytes = C.c_size_t(0)
     _lib.check(lib().dvf_jacobian_workspace_bytes(n, D, M, C.byref(nbytes)))
-    # workspace from torch's caching allocator (stream-ordered reuse, no driver allocation in the steady state)
-    ws = torch.empty((nbytes.value + 7) // 8, dtype=torch.float64, device="cuda") if nbytes.value else None
+    ws = _workspace(nbytes.value) if nbytes.value else None
     _lib.check(lib().dvf_jacobian_ws(ptr(x), n, D, ptr(Xc), M, float(beta), ptr(Cm), ptr(J), ptr(ws), nbytes.value,
                                      stream_ptr()))
     return J
@@ -103,12 +122,22 @@ def _side_stream():
     return _SIDE[d]
 
 
-def div_acc_curv(x, Xc, beta, Cm, formula=2, want=("v", "div", "acc", "acc_norm", "curv", "curv_norm")):
-    """K7 -- reference vectorfield/utils.py:699-821; returns a dict of the requested outputs."""
+def div_acc_curv(x, Xc, beta, Cm, formula=2, want=("v", "div", "acc", "acc_norm", "curv", "curv_norm"), out=None):
+    """K7 -- reference vectorfield/utils.py:699-821; returns a dict of the requested outputs.  `out`: a dict returned
+    by an earlier call for the same n, D, `want` -- its tensors are overwritten instead of allocating new ones."""
     x, Xc, Cm = _field(x, Xc, Cm)
     n, D = x.shape
     shapes = {"v": (n, D), "div": (n,), "acc": (n, D), "acc_norm": (n,), "curv": (n, D), "curv_norm": (n,)}
-    out = {k: (empty(shapes[k]) if k in want else None) for k in shapes}
+    if out is not None:
+        for k in shapes:
+            if (k in want) != (out.get(k) is not None) and not (k == "curv" and formula == 1):
+                raise ValueError("out does not hold the requested outputs")
+            if out.get(k) is not None and (tuple(out[k].shape) != shapes[k] or out[k].dtype != torch.float64
+                                           or not out[k].is_cuda or not out[k].is_contiguous()):
+                raise ValueError("out[%r] must be a contiguous float64 CUDA tensor of shape %s" % (k, shapes[k]))
+        out = dict(out)
+    else:
+        out = {k: (empty(shapes[k]) if k in want else None) for k in shapes}
     if formula == 1:
         out["curv"] = None
     _lib.check(lib().dvf_div_acc_curv(ptr(x), n, D, ptr(Xc), Xc.shape[0], float(beta), ptr(Cm), int(formula),

@@ -86,6 +86,33 @@ def unique_rows(X: torch.Tensor):
     return X[first], first
 
 
+def _pairwise_rows(sq, lo, n):
+    """NumPy's pairwise_sum over rows lo .. lo+n-1 of sq (one row per summand).  Module level on purpose: as a nested
+    recursive function it formed a reference cycle (function <-> its own closure cell) that kept `sq`, the size of
+    the whole velocity matrix, alive until the cyclic collector ran -- the caching allocator then saw a different
+    set of free blocks every step and went to cudaMalloc at random moments (tens of ms of idle GPU)."""
+    if n < 8:
+        res = torch.zeros_like(sq[0])
+        for i in range(n):
+            res = res + sq[lo + i]
+        return res
+    if n <= 128:
+        r = [sq[lo + j].clone() for j in range(8)]
+        i = 8
+        while i < n - (n % 8):
+            for j in range(8):
+                r[j] += sq[lo + i + j]
+            i += 8
+        res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]))
+        while i < n:
+            res = res + sq[lo + i]
+            i += 1
+        return res
+    n2 = n // 2
+    n2 -= n2 % 8
+    return _pairwise_rows(sq, lo, n2) + _pairwise_rows(sq, lo + n2, n - n2)
+
+
 def row_norms(Y: torch.Tensor) -> torch.Tensor:
     """np.linalg.norm(Y, axis=1) = sqrt(add.reduce(Y*Y, axis=1)) with NumPy's summation order along a contiguous
     row (pairwise_sum: straight loop below 8 terms, else 8 interleaved partial sums combined as
@@ -94,30 +121,7 @@ def row_norms(Y: torch.Tensor) -> torch.Tensor:
     and the whole matrix give the same bits."""
     Yt = Y.T.contiguous()
     sq = Yt * Yt
-
-    def pairwise(lo, n):
-        if n < 8:
-            res = torch.zeros_like(sq[0])
-            for i in range(n):
-                res = res + sq[lo + i]
-            return res
-        if n <= 128:
-            r = [sq[lo + j].clone() for j in range(8)]
-            i = 8
-            while i < n - (n % 8):
-                for j in range(8):
-                    r[j] += sq[lo + i + j]
-                i += 8
-            res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]))
-            while i < n:
-                res = res + sq[lo + i]
-                i += 1
-            return res
-        n2 = n // 2
-        n2 -= n2 % 8
-        return pairwise(lo, n2) + pairwise(lo + n2, n - n2)
-
-    ss = pairwise(0, Yt.shape[0])
+    ss = _pairwise_rows(sq, 0, Yt.shape[0])
     # CUDA's double sqrt is correctly rounded like NumPy's; torch's vectorised CPU sqrt is not (CPU = tests only)
     return torch.sqrt(ss) if ss.is_cuda else torch.from_numpy(np.sqrt(ss.numpy()))
 

@@ -130,3 +130,32 @@ def test_threaded_cumsum_is_numpy_cumsum_bit_for_bit():
     p[skip] = 0.0
     assert np.array_equal(np.cumsum(p), _host_cumsum(v, total, skip))
     assert np.array_equal(np.cumsum(v / total), _host_cumsum(v, total))
+
+
+def test_row_norms_leaves_no_cyclic_garbage():
+    """row_norms' temporaries (two copies of the velocity matrix) must die by reference count when it returns.  A
+    nested recursive helper once tied them into a reference cycle; on the GPU they then came back to the caching
+    allocator only when the cyclic collector happened to run, and the benchmark loop hit cudaMalloc at random."""
+    import gc
+    import weakref
+
+    Y = torch.from_numpy(np.random.default_rng(0).normal(size=(500, 30)))
+    seen = []
+    orig = torch.Tensor.__mul__
+
+    def spy(self, *a, **k):
+        out = orig(self, *a, **k)
+        if out.shape == (30, 500):            # the squared, transposed velocity matrix
+            seen.append(weakref.ref(out))
+        return out
+
+    gc.collect()
+    gc.disable()
+    try:
+        torch.Tensor.__mul__ = spy
+        ref = np.linalg.norm(Y.numpy(), axis=1)
+        assert np.array_equal(prelude.row_norms(Y).numpy(), ref)
+    finally:
+        torch.Tensor.__mul__ = orig
+        gc.enable()
+    assert seen and all(r() is None for r in seen)
