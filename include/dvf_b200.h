@@ -286,7 +286,8 @@ int dvf_host_scale(const double* v, int64_t n, double total, double* p);
  * recursion run on threads).  tools/sampling.py:244 (np.sum(tmp_V)). */
 int dvf_host_pairwise_sum(const double* a, int64_t n, double* out);
 /* raw[i] = sequential cumulative sum of p_k = v[k] / total, with p_k = 0 for the ascending indices in `skip`
- * (the cells already drawn): Generator.choice(replace=False)'s cumsum(p) without storing p. */
+ * (the cells already drawn): Generator.choice(replace=False)'s cumsum(p) without storing p.  Every partial sum has the
+ * bits of numpy.cumsum's sequential recurrence; the work is spread over host threads (csrc/host_cumsum.cpp). */
 int dvf_host_choice_cumsum(const double* v, int64_t n, double total, const int64_t* skip, int64_t n_skip, double* raw);
 /* out[q] = searchsorted(raw / raw[n-1], x[q], side='right') by bisection on the fly (no quotient array). */
 int dvf_host_searchsorted_div(const double* raw, int64_t n, const double* x, int64_t m, int64_t* out);
