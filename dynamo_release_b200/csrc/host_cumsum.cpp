@@ -19,6 +19,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstring>
+#include <exception>
 #include <thread>
 #include <vector>
 #if defined(__x86_64__)
@@ -250,10 +251,28 @@ void host_scaled_cumsum(const double* v, bool divide, double total, const int64_
             recurrence(raw, blk_lo(b), blk_hi(b), s);
         }
     };
+    // helpers wait for `go`: if the host refuses a thread, the ones already started are released unused and the
+    // whole array takes the serial path (nothing has been written yet)
+    std::atomic<int> go{0};
     std::vector<std::thread> th;
-    for (int t = 1; t < nt; ++t) th.emplace_back(worker, t);
-    worker(0);
+    bool spawned = true;
+    try {
+        for (int t = 1; t < nt; ++t)
+            th.emplace_back([&, t] {
+                int g;
+                while ((g = go.load(std::memory_order_acquire)) == 0) std::this_thread::yield();
+                if (g == 1) worker(t);
+            });
+    } catch (const std::exception&) {
+        spawned = false;
+    }
+    go.store(spawned ? 1 : 2, std::memory_order_release);
+    if (spawned) worker(0);
     for (auto& x : th) x.join();
+    if (!spawned) {
+        double acc = 0.0;
+        for (int64_t b = 0; b < nb; ++b) { prepare(b); recurrence(raw, blk_lo(b), blk_hi(b), acc); }
+    }
 }
 
 }  // namespace dvf
