@@ -153,7 +153,8 @@ def velocity_weighted_choice(speed: np.ndarray, M: int, seed: int) -> np.ndarray
     algorithm (numpy/random/_generator.pyx: draw uniforms, cdf = cumsum(p) / cdf[-1], searchsorted(side='right'),
     keep first occurrences, zero the found entries and repeat) with its O(n) passes reduced to what the result
     needs, each bit-identical to NumPy's: total = np.sum(speed) by the same pairwise tree (dvf_host_pairwise_sum),
-    the strictly sequential cumulative sum of speed / total with the found cells skipped (dvf_host_choice_cumsum;
+    the cumulative sum of speed / total with the found cells skipped, every partial sum rounded as in NumPy's
+    sequential recurrence but formed on several threads (dvf_host_choice_cumsum -> csrc/host_cumsum.cpp;
     p itself is never stored), and the bisection evaluated on raw[i] / raw[-1] on the fly
     (dvf_host_searchsorted_div; the normalised array is never formed).  The chosen cells are identical --
     tests/test_prelude_cpu.py checks them against Generator.choice itself."""
